@@ -1,0 +1,144 @@
+/*
+ * fa_b200.h — C ABI of the B200-native flash-attention forward library (libfa_b200.so).
+ *
+ * This is the drop-in boundary: a torch-free shared library whose three entry points
+ * replace the three ops the reference exports through pybind11
+ * (reference csrc/flash_attn/flash_api.cpp:939-946):
+ *
+ *   fa_b200_fwd          <-  mha_fwd          (flash_api.cpp:240-420)
+ *   fa_b200_varlen_fwd   <-  mha_varlen_fwd   (flash_api.cpp:422-669)
+ *   fa_b200_fwd_kvcache  <-  mha_fwd_kvcache  (flash_api.cpp:671-937)
+ *
+ * All three take one POD parameter block (the analogue of Flash_fwd_params,
+ * reference csrc/flash_attn/src/flash.h:51-141): raw device pointers, int64 strides in
+ * ELEMENTS, plain ints.  No torch types, no allocation: the caller owns every buffer,
+ * including the split-KV workspace whose size fa_b200_workspace_bytes() reports.
+ * Kernels are enqueued on the given stream; nothing synchronises the host.
+ *
+ * Error convention: 0 on success, a negative FA_ERR_* code otherwise; the message
+ * (same wording as the reference's TORCH_CHECK text where one exists) is retrievable
+ * per thread with fa_b200_last_error().  The Python shim raises RuntimeError from it,
+ * matching the reference's c10::Error -> RuntimeError behaviour (flash_api.cpp:16-18).
+ */
+#ifndef FA_B200_H_
+#define FA_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FA_B200_ABI_VERSION 1
+
+enum {
+  FA_OK = 0,
+  FA_ERR_INVALID = -1,     /* argument validation failed (reference: TORCH_CHECK) */
+  FA_ERR_UNSUPPORTED = -2, /* valid in the reference, not built here */
+  FA_ERR_CUDA = -3,        /* CUDA runtime / launch error */
+  FA_ERR_WORKSPACE = -4    /* workspace too small */
+};
+
+/* Which kernel family served the call (written to FaFwdParams.kernel_used). */
+enum {
+  FA_KERNEL_NONE = 0,
+  FA_KERNEL_TC5_PREFILL = 1, /* tcgen05 + TMA + TMEM warp-specialised kernel */
+  FA_KERNEL_TILE = 2,        /* mma.sync 64-row tile kernel (all features) */
+  FA_KERNEL_DECODE = 3       /* GQA-packed paged split-KV decode kernel */
+};
+
+typedef struct FaFwdParams {
+  /* ---- tensors (device pointers), strides in elements ---- */
+  const void* q;  /* dense (b,sq,h,d) | varlen (total_q,h,d) */
+  const void* k;  /* dense (b,sk,hk,d) | varlen (total_k,hk,d) | paged (num_blocks,page,hk,d) */
+  const void* v;
+  void* o;        /* same shape as q */
+  float* softmax_lse; /* (b,h,sq) fp32; varlen: (b,h,max_seqlen_q) (flash_api.cpp:348,578) */
+  int64_t q_batch_stride, q_row_stride, q_head_stride;
+  int64_t k_batch_stride, k_row_stride, k_head_stride; /* paged: batch stride = per-block stride */
+  int64_t v_batch_stride, v_row_stride, v_head_stride;
+  int64_t o_batch_stride, o_row_stride, o_head_stride;
+
+  /* ---- sizes ---- */
+  int32_t b;         /* batch */
+  int32_t seqlen_q;  /* dense: sq; varlen: max_seqlen_q */
+  int32_t seqlen_k;  /* dense: sk; varlen: max_seqlen_k; paged kvcache: max_blocks*page */
+  int32_t h, h_k, d;
+  int32_t is_bf16;   /* 1 = bf16, 0 = fp16 */
+  float softmax_scale;
+
+  /* ---- masking ---- */
+  int32_t is_causal;
+  int32_t window_left, window_right; /* -1 = unbounded */
+  const float* alibi_slopes;         /* (h) or (b,h) fp32, or NULL */
+  int64_t alibi_slopes_batch_stride; /* 0 when (h) */
+
+  /* ---- varlen / kv-cache ---- */
+  const int32_t* cu_seqlens_q; /* (b+1) or NULL */
+  const int32_t* cu_seqlens_k; /* (b+1) cumulative, or (b) lengths if !is_seqlens_k_cumulative */
+  const int32_t* seqused_k;    /* (b) or NULL */
+  int32_t is_seqlens_k_cumulative;
+  const int32_t* block_table;  /* (b,max_blocks_per_seq) int32 or NULL */
+  int64_t block_table_batch_stride;
+  int32_t page_block_size;
+  int32_t max_blocks_per_seq;
+  int32_t num_blocks;          /* size of the page pool (bounds check / tensor maps) */
+  const int32_t* cache_batch_idx; /* (b) or NULL */
+  int64_t total_q, total_k;    /* varlen: rows in q / k (tensor-map bounds) */
+
+  /* ---- append-KV + rotary (fwd_kvcache only) ---- */
+  const void* knew; const void* vnew; /* (b,seqlen_knew,hk,d) or NULL */
+  int64_t knew_batch_stride, knew_row_stride, knew_head_stride;
+  int64_t vnew_batch_stride, vnew_row_stride, vnew_head_stride;
+  int32_t seqlen_knew;
+  const void* rotary_cos; const void* rotary_sin; /* (seqlen_ro, rotary_dim/2) */
+  int32_t rotary_dim, seqlen_ro, is_rotary_interleaved;
+
+  /* ---- split-KV ---- */
+  int32_t num_splits;    /* in: 0 = heuristic, >=1 forced; out: splits used */
+  void* workspace;       /* >= fa_b200_workspace_bytes(p) bytes, or NULL when that is 0 */
+  size_t workspace_bytes;
+
+  /* ---- tuning / diagnostics ---- */
+  int32_t num_sms;       /* 0 = query the device */
+  int32_t force_kernel;  /* 0 = auto, else FA_KERNEL_* (tests) */
+  int32_t kernel_used;   /* out */
+  int32_t launches;      /* out: kernels launched by this call */
+} FaFwdParams;
+
+/* ABI version of the loaded library (== FA_B200_ABI_VERSION). */
+int fa_b200_abi_version(void);
+/* sizeof(FaFwdParams) as compiled; the binding checks it against its own mirror. */
+size_t fa_b200_params_size(void);
+/* Thread-local message of the last failing call on this thread ("" if none). */
+const char* fa_b200_last_error(void);
+
+/* Split choice for (batch*heads*m_blocks, SMs, n_blocks): the reference's wave-efficiency
+ * rule, num_splits_heuristic (flash_api.cpp:158-192). Pure host function. */
+int fa_b200_num_splits_heuristic(int batch_nheads_mblocks, int num_sms, int num_n_blocks,
+                                 int max_splits);
+
+/* Bytes of split-KV workspace the call described by *p needs (0 if it will not split).
+ * `op` is 0 = fwd, 1 = varlen_fwd, 2 = fwd_kvcache.  Resolves p->num_splits==0 with the
+ * heuristic exactly as the launch will.  Returns (size_t)-1 on invalid arguments. */
+size_t fa_b200_workspace_bytes(const FaFwdParams* p, int op);
+
+/* The three ops.  `stream` is a cudaStream_t passed as void*. */
+int fa_b200_fwd(FaFwdParams* p, void* stream);
+int fa_b200_varlen_fwd(FaFwdParams* p, void* stream);
+int fa_b200_fwd_kvcache(FaFwdParams* p, void* stream);
+
+/* Merge `n` partial results (o_part: (n,rows,d) fp32 or bf16/fp16, lse_part: (n,rows) fp32)
+ * into o (rows,d) + lse (rows): lse = logsumexp_s lse_s, o = sum_s exp(lse_s-lse) o_s.
+ * Same algebra as combine_attn_seqk_parallel (flash_fwd_kernel.h:1092-1250); used for the
+ * in-GPU split-KV merge and for the cross-GPU (out,lse) merge after an allgather.
+ * part_dtype / out_dtype: 0 = fp32, 1 = bf16, 2 = fp16. */
+int fa_b200_combine(const void* o_part, const float* lse_part, void* o, float* lse,
+                    int32_t n, int64_t rows, int32_t d, int32_t part_dtype, int32_t out_dtype,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FA_B200_H_ */

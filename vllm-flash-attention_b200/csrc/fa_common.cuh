@@ -1,0 +1,132 @@
+// fa_common.cuh — device-side parameter block and sm_100a PTX wrappers shared by the kernels.
+//
+// KParams is the resolved form of FaFwdParams (include/fa_b200.h) after the host glue
+// (fa_api.cu) has applied the reference's normalisation rules (flash_api.cpp:289-294,
+// :119-126).  It plays the role of Flash_fwd_params (reference src/flash.h:51-141).
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace fa {
+
+struct KParams {
+  const void* q; const void* k; const void* v; void* o;
+  float* lse;             // (b,h,seqlen_q) fp32
+  float* o_accum;         // (splits,b,h,seqlen_q,d) fp32 — split partials
+  float* lse_accum;       // (splits,b,h,seqlen_q)
+  int64_t q_batch_stride, q_row_stride, q_head_stride;
+  int64_t k_batch_stride, k_row_stride, k_head_stride;
+  int64_t v_batch_stride, v_row_stride, v_head_stride;
+  int64_t o_batch_stride, o_row_stride, o_head_stride;
+  int b, seqlen_q, seqlen_k, h, h_k, d, group;  // group = h / h_k
+  float scale, scale_log2;                      // softmax_scale, softmax_scale*log2(e)
+  int is_causal, is_local;                      // local: window applies and not pure causal
+  int window_left, window_right;                // normalised as set_params_fprop does
+  const float* alibi_slopes; int64_t alibi_batch_stride;
+  const int* cu_seqlens_q; const int* cu_seqlens_k; const int* seqused_k;
+  int is_seqlens_k_cumulative;
+  const int* block_table; int64_t block_table_batch_stride; int page_block_size;
+  int max_blocks_per_seq; int num_blocks;
+  const int* cache_batch_idx;
+  int seqlen_knew;                              // keys appended this call (already in cache)
+  int num_splits;
+  int lse_seq_stride;                           // seqlen_q used for lse/accum row indexing
+};
+
+// Per-sequence geometry — the analogue of BlockInfo (reference src/block_info.h:11-42).
+struct SeqInfo {
+  int sq, sk;            // actual lengths
+  int64_t q_off, k_off, v_off;  // element offsets of row 0 (paged: k_off/v_off unused)
+  int kv_batch;          // batch index into a non-paged cache
+  __device__ __forceinline__ SeqInfo(const KParams& p, int bidb) {
+    if (p.cu_seqlens_q) {
+      int s0 = p.cu_seqlens_q[bidb];
+      sq = p.cu_seqlens_q[bidb + 1] - s0;
+      q_off = (int64_t)s0 * p.q_row_stride;
+    } else {
+      sq = p.seqlen_q;
+      q_off = (int64_t)bidb * p.q_batch_stride;
+    }
+    kv_batch = p.cache_batch_idx ? p.cache_batch_idx[bidb] : bidb;
+    if (p.cu_seqlens_k) {
+      if (p.is_seqlens_k_cumulative) {
+        int s0 = p.cu_seqlens_k[bidb];
+        sk = p.cu_seqlens_k[bidb + 1] - s0;
+        k_off = (int64_t)s0 * p.k_row_stride; v_off = (int64_t)s0 * p.v_row_stride;
+      } else {
+        sk = p.cu_seqlens_k[bidb] + p.seqlen_knew;
+        k_off = (int64_t)kv_batch * p.k_batch_stride; v_off = (int64_t)kv_batch * p.v_batch_stride;
+      }
+    } else {
+      sk = p.seqlen_k;
+      k_off = (int64_t)kv_batch * p.k_batch_stride; v_off = (int64_t)kv_batch * p.v_batch_stride;
+    }
+    if (p.seqused_k) sk = p.seqused_k[bidb];
+  }
+};
+
+// Output row offsets (o uses the same row indexing as q).
+__device__ __forceinline__ int64_t o_seq_offset(const KParams& p, int bidb) {
+  return p.cu_seqlens_q ? (int64_t)p.cu_seqlens_q[bidb] * p.o_row_stride
+                        : (int64_t)bidb * p.o_batch_stride;
+}
+
+// ---------------------------------------------------------------------------------------
+// dtype helpers
+template <typename T> struct Pack2;
+template <> struct Pack2<__nv_bfloat16> {
+  static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
+    uint32_t r; asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo)); return r;
+  }
+};
+template <> struct Pack2<__half> {
+  static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
+    uint32_t r; asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo)); return r;
+  }
+};
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y;
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// ---------------------------------------------------------------------------------------
+// cp.async (LDGSTS) 16-byte, zero-fill when !pred
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool pred) {
+  int sz = pred ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N));
+}
+
+// ldmatrix / mma.sync (legacy tensor path — used by the HBM-bound decode kernel and the
+// feature-complete tile kernel; the compute-bound prefill kernel uses tcgen05 below)
+__device__ __forceinline__ void ldsm_x4(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t addr, uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+template <typename T> __device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1);
+template <> __device__ __forceinline__ void mma16816<__nv_bfloat16>(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <> __device__ __forceinline__ void mma16816<__half>(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+}  // namespace fa

@@ -1,0 +1,316 @@
+// fa_decode.cu — GQA-packed, paged, split-KV decode kernel (HBM-bound).
+//
+// Replaces compute_attn_1rowblock_splitkv (reference src/flash_fwd_kernel.h:474-1053) for the
+// decode shape: few query rows (seqlen_q * group <= 16*MT) against a long (paged) KV cache.
+//
+// Design (not the reference's): one CTA per (split, kv_head, sequence).  All `group` query heads
+// that share the KV head (times seqlen_q positions) are packed as the M rows of one m16 MMA tile,
+// so K/V are streamed from HBM exactly once per KV head (the reference gets this through the
+// seqlenq_ngroups_swapped reshape, flash_api.cpp:298-304).  The KV range of the CTA is cut into
+// 16-row chunks (one page when page_block_size==16; never straddles a page since page%16==0,
+// flash_api.cpp:491,735).  Chunks are dealt round-robin to the warps; EVERY WARP RUNS ITS OWN
+// cp.async ring (STAGES deep) and its own online softmax over its chunks — no block-wide barrier
+// in the streaming loop — and the NW per-warp (m,l,O) states are merged once at the end in a
+// fixed order (bitwise deterministic).  The page id of chunk i+1 is fetched while chunk i is
+// being issued, so the block_table indirection (reference src/utils.h:297-315) is off the
+// critical path.  Loads are 16 B cp.async, 2 full 256 B rows per warp instruction.
+#include "fa_common.cuh"
+#include "fa_warp_attn.cuh"
+#include "fa_launch.h"
+
+namespace fa {
+
+template <typename T, int D, int MT, int NW, int STAGES>
+struct DecodeCfg {
+  static constexpr int ROWS = 16 * MT;
+  static constexpr int CHUNK = 16;
+  static constexpr int TILE_BYTES = CHUNK * D * 2;             // one K (or V) chunk
+  static constexpr int Q_BYTES = ROWS * D * 2;
+  static constexpr int RING_BYTES = NW * STAGES * 2 * TILE_BYTES;
+  static constexpr int RED_STRIDE = D + 8;                      // floats
+  static constexpr int RED_BYTES = ROWS * RED_STRIDE * 4;
+  static constexpr int STAT_BYTES = (2 * NW + 2) * ROWS * 4;    // m[NW][ROWS], l[NW][ROWS], inv_l, lse
+  static constexpr int MAIN_BYTES = RING_BYTES > RED_BYTES ? RING_BYTES : RED_BYTES;
+  static constexpr int SMEM = Q_BYTES + MAIN_BYTES + STAT_BYTES;
+};
+
+template <typename T, int D, int MT, int NW, int STAGES>
+__global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constant__ KParams p) {
+  using Cfg = DecodeCfg<T, D, MT, NW, STAGES>;
+  constexpr int ROWS = Cfg::ROWS;
+  constexpr int CPR = D / 8;  // 16 B chunks per row
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* q_sm = smem;
+  uint8_t* ring = smem + Cfg::Q_BYTES;
+  float* stat_m = reinterpret_cast<float*>(smem + Cfg::Q_BYTES + Cfg::MAIN_BYTES);
+  float* stat_l = stat_m + NW * ROWS;
+  float* row_inv = stat_l + NW * ROWS;
+  float* row_lse = row_inv + ROWS;
+
+  const int split = blockIdx.x, kvh = blockIdx.y, bidb = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = p.group;
+  const SeqInfo si(p, bidb);
+  const int sq = si.sq, sk = si.sk;
+  const int R = sq * g;  // live packed rows: r = qpos*g + head_in_group
+  if (sq <= 0) return;
+
+  // ---- KV chunk range of this CTA ----
+  const RowWindow w_first = row_window(p, 0, sq, sk), w_last = row_window(p, sq - 1, sq, sk);
+  const int c_lo = max(w_first.lo, 0) / 16;
+  const int c_hi = (max(w_last.hi, 0) + 15) / 16;
+  const int n_chunks = max(c_hi - c_lo, 0);
+  const int per_split = (n_chunks + p.num_splits - 1) / p.num_splits;
+  const int c_begin = c_lo + split * per_split;
+  const int c_end = min(c_hi, c_begin + per_split);
+
+  // ---- Q: gather the packed rows into shared memory (zero rows beyond R) ----
+  {
+    const T* qb = reinterpret_cast<const T*>(p.q) + si.q_off;
+    for (int idx = threadIdx.x; idx < ROWS * CPR; idx += NW * 32) {
+      int r = idx / CPR, c = idx % CPR;
+      int qpos = r / g, hg = r - qpos * g;
+      const T* src = qb + (int64_t)qpos * p.q_row_stride + (int64_t)(kvh * g + hg) * p.q_head_stride + c * 8;
+      cp_async16(smem_u32(q_sm) + swz<D>(r, c), r < R ? (const void*)src : (const void*)qb, r < R);
+    }
+    cp_async_commit();
+  }
+
+  // ---- per-thread row metadata (window, ALiBi) for its 2*MT rows ----
+  int row_lo[MT][2], row_hi[MT][2], row_shift[MT][2];
+  float row_slope[MT][2];
+  const bool has_alibi = p.alibi_slopes != nullptr;
+#pragma unroll
+  for (int i = 0; i < MT; i++)
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+      int row = i * 16 + (lane >> 2) + r * 8;
+      int qpos = min(row / g, sq - 1), hg = row % g;
+      RowWindow w = row_window(p, qpos, sq, sk);
+      row_lo[i][r] = w.lo; row_hi[i][r] = w.hi; row_shift[i][r] = qpos + sk - sq;
+      row_slope[i][r] = has_alibi
+          ? p.alibi_slopes[bidb * p.alibi_batch_stride + kvh * g + hg] * 1.4426950408889634f : 0.f;
+    }
+  const int hi_min = w_first.hi, lo_max = w_last.lo;
+
+  // ---- K/V addressing ----
+  const T* kbase = reinterpret_cast<const T*>(p.k) + (int64_t)kvh * p.k_head_stride;
+  const T* vbase = reinterpret_cast<const T*>(p.v) + (int64_t)kvh * p.v_head_stride;
+  const bool paged = p.block_table != nullptr;
+  const int* table = paged ? p.block_table + (int64_t)bidb * p.block_table_batch_stride : nullptr;
+  if (!paged) { kbase += si.k_off; vbase += si.v_off; }
+  const int page = p.page_block_size;
+  auto page_of = [&](int c) -> int {  // physical block id of chunk c (clamped: SURVEY 5a.8)
+    int pg = min((c * 16) / page, p.max_blocks_per_seq - 1);
+    return table[pg];
+  };
+
+  uint8_t* my_ring = ring + warp * (STAGES * 2 * Cfg::TILE_BYTES);
+  auto issue = [&](int c, int stage, int blk) {
+    const int row0 = c * 16;
+    int64_t koff, voff;
+    if (paged) {
+      int in_page = row0 % page;
+      koff = (int64_t)blk * p.k_batch_stride + (int64_t)in_page * p.k_row_stride;
+      voff = (int64_t)blk * p.v_batch_stride + (int64_t)in_page * p.v_row_stride;
+    } else {
+      koff = (int64_t)row0 * p.k_row_stride;
+      voff = (int64_t)row0 * p.v_row_stride;
+    }
+    uint32_t ks = smem_u32(my_ring + stage * 2 * Cfg::TILE_BYTES);
+    uint32_t vs = ks + Cfg::TILE_BYTES;
+#pragma unroll
+    for (int it = 0; it < (16 * CPR) / 32; it++) {
+      int seg = it * 32 + lane;
+      int r = seg / CPR, cc = seg % CPR;
+      bool ok = row0 + r < sk;
+      int rr = ok ? r : 0;
+      cp_async16(ks + swz<D>(r, cc), kbase + koff + (int64_t)rr * p.k_row_stride + cc * 8, ok);
+      cp_async16(vs + swz<D>(r, cc), vbase + voff + (int64_t)rr * p.v_row_stride + cc * 8, ok);
+    }
+  };
+
+  WarpAttn<T, D, MT, 16> attn;
+  attn.init();
+
+  const int first = c_begin + warp;
+  const int n_mine = first < c_end ? (c_end - first + NW - 1) / NW : 0;
+
+  // prologue: STAGES-1 chunks in flight
+  int blk_next = 0;
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; s++) {
+    if (s < n_mine) {
+      int c = first + s * NW;
+      issue(c, s, paged ? page_of(c) : 0);
+    }
+    cp_async_commit();
+  }
+  if (paged && STAGES - 1 < n_mine) blk_next = page_of(first + (STAGES - 1) * NW);
+
+  const uint32_t q_s = smem_u32(q_sm);
+  // Q visible to all warps
+  cp_async_wait<STAGES - 1>();   // Q group is the oldest
+  __syncthreads();
+
+  for (int i = 0; i < n_mine; i++) {
+    const int c = first + i * NW;
+    {  // refill the stage consumed in the previous iteration
+      int inext = i + STAGES - 1;
+      if (inext < n_mine) {
+        issue(first + inext * NW, inext % STAGES, blk_next);
+        if (paged && inext + 1 < n_mine) blk_next = page_of(first + (inext + 1) * NW);
+      }
+      cp_async_commit();
+    }
+    cp_async_wait<STAGES - 1>();
+    __syncwarp();
+    const int stage = i % STAGES;
+    const uint32_t ks = smem_u32(my_ring + stage * 2 * Cfg::TILE_BYTES);
+    const int col0 = c * 16;
+    const bool need_mask = has_alibi || (col0 + 16 > hi_min) || (col0 < lo_max);
+    attn.step(q_s, ks, ks + Cfg::TILE_BYTES, p.scale_log2, need_mask,
+              [&](int row, int col, float x) -> float {
+                const int i2 = row >> 4, r2 = (row >> 3) & 1;
+                const int j = col0 + col;
+                if (has_alibi) x -= row_slope[i2][r2] * fabsf((float)(row_shift[i2][r2] - j));
+                return (j >= row_lo[i2][r2] && j < row_hi[i2][r2]) ? x : -INFINITY;
+              });
+    __syncwarp();
+  }
+  attn.finish_sums();
+  cp_async_wait<0>();
+
+  // ---- merge the NW warp states (fixed order => deterministic) ----
+  if ((lane & 3) == 0) {
+#pragma unroll
+    for (int i = 0; i < MT; i++)
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        int row = i * 16 + (lane >> 2) + r * 8;
+        stat_m[warp * ROWS + row] = attn.m[i][r];
+        stat_l[warp * ROWS + row] = attn.l[i][r];
+      }
+  }
+  __syncthreads();   // also: every warp is done with its ring -> reuse as the reduction buffer
+  float my_scale[MT][2];
+#pragma unroll
+  for (int i = 0; i < MT; i++)
+#pragma unroll
+    for (int r = 0; r < 2; r++) {
+      int row = i * 16 + (lane >> 2) + r * 8;
+      float mt = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < NW; w++) mt = fmaxf(mt, stat_m[w * ROWS + row]);
+      float lt = 0.f;
+#pragma unroll
+      for (int w = 0; w < NW; w++) {
+        float mw = stat_m[w * ROWS + row];
+        lt += mw == -INFINITY ? 0.f : stat_l[w * ROWS + row] * fast_exp2(mw - mt);
+      }
+      my_scale[i][r] = attn.m[i][r] == -INFINITY ? 0.f : fast_exp2(attn.m[i][r] - mt);
+      if (warp == 0 && (lane & 3) == 0) {
+        const bool empty = !(lt > 0.f);
+        row_inv[row] = empty ? 0.f : 1.f / lt;
+        // natural-log LSE = max*scale + ln(sum) (softmax.h:179); m is in log2 units
+        row_lse[row] = empty ? (p.num_splits > 1 ? -INFINITY : INFINITY)
+                             : mt * 0.6931471805599453f + __logf(lt);
+      }
+    }
+  float* red = reinterpret_cast<float*>(ring);
+  for (int w = 0; w < NW; w++) {
+    if (warp == w) {
+#pragma unroll
+      for (int i = 0; i < MT; i++)
+#pragma unroll
+        for (int j = 0; j < D / 8; j++)
+#pragma unroll
+          for (int r = 0; r < 2; r++) {
+            int row = i * 16 + (lane >> 2) + r * 8;
+            float2* dst = reinterpret_cast<float2*>(red + row * Cfg::RED_STRIDE + j * 8 + (lane & 3) * 2);
+            float2 val = make_float2(attn.o[i][j][2 * r] * my_scale[i][r], attn.o[i][j][2 * r + 1] * my_scale[i][r]);
+            if (w > 0) { float2 old = *dst; val.x += old.x; val.y += old.y; }
+            *dst = val;
+          }
+    }
+    __syncthreads();
+  }
+
+  // ---- write out ----
+  const int Rw = min(R, ROWS);
+  if (p.num_splits > 1) {
+    // fp32 partials, (split, b, h, sq[, d]) like the reference's accum buffers (flash_api.cpp:212-213)
+    for (int idx = threadIdx.x; idx < Rw * (D / 4); idx += NW * 32) {
+      int r = idx / (D / 4), c4 = idx % (D / 4);
+      int qpos = r / g, hg = r - qpos * g;
+      int64_t orow = (((int64_t)split * p.b + bidb) * p.h + kvh * g + hg) * p.lse_seq_stride + qpos;
+      float inv = row_inv[r];
+      float4 x = *reinterpret_cast<const float4*>(red + r * Cfg::RED_STRIDE + c4 * 4);
+      x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
+      *reinterpret_cast<float4*>(p.o_accum + orow * D + c4 * 4) = x;
+    }
+    for (int r = threadIdx.x; r < Rw; r += NW * 32) {
+      int qpos = r / g, hg = r - qpos * g;
+      int64_t orow = (((int64_t)split * p.b + bidb) * p.h + kvh * g + hg) * p.lse_seq_stride + qpos;
+      p.lse_accum[orow] = row_lse[r];
+    }
+  } else {
+    T* ob = reinterpret_cast<T*>(p.o) + o_seq_offset(p, bidb);
+    for (int idx = threadIdx.x; idx < Rw * CPR; idx += NW * 32) {
+      int r = idx / CPR, c = idx % CPR;
+      int qpos = r / g, hg = r - qpos * g;
+      float inv = row_inv[r];
+      const float* src = red + r * Cfg::RED_STRIDE + c * 8;
+      float4 a = *reinterpret_cast<const float4*>(src), b2 = *reinterpret_cast<const float4*>(src + 4);
+      uint4 pk;
+      pk.x = Pack2<T>::pack(a.x * inv, a.y * inv); pk.y = Pack2<T>::pack(a.z * inv, a.w * inv);
+      pk.z = Pack2<T>::pack(b2.x * inv, b2.y * inv); pk.w = Pack2<T>::pack(b2.z * inv, b2.w * inv);
+      *reinterpret_cast<uint4*>(ob + (int64_t)qpos * p.o_row_stride + (int64_t)(kvh * g + hg) * p.o_head_stride + c * 8) = pk;
+    }
+    if (p.lse) {
+      for (int r = threadIdx.x; r < Rw; r += NW * 32) {
+        int qpos = r / g, hg = r - qpos * g;
+        p.lse[((int64_t)bidb * p.h + kvh * g + hg) * p.lse_seq_stride + qpos] = row_lse[r];
+      }
+    }
+  }
+}
+
+template <typename T, int D, int MT, int NW, int STAGES>
+static cudaError_t launch_decode_t(const KParams& p, cudaStream_t stream) {
+  using Cfg = DecodeCfg<T, D, MT, NW, STAGES>;
+  auto kern = fa_decode_kernel<T, D, MT, NW, STAGES>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
+  if (e != cudaSuccess) return e;
+  dim3 grid(p.num_splits, p.h_k, p.b);
+  kern<<<grid, NW * 32, Cfg::SMEM, stream>>>(p);
+  return cudaGetLastError();
+}
+
+template <typename T>
+static cudaError_t launch_decode_d(const KParams& p, int mt, cudaStream_t stream) {
+  if (p.d == 64) {
+    if (mt == 1) return launch_decode_t<T, 64, 1, 4, 6>(p, stream);
+    if (mt == 2) return launch_decode_t<T, 64, 2, 4, 6>(p, stream);
+  } else if (p.d == 128) {
+    if (mt == 1) return launch_decode_t<T, 128, 1, 4, 3>(p, stream);
+    if (mt == 2) return launch_decode_t<T, 128, 2, 4, 3>(p, stream);
+  } else if (p.d == 256) {
+    if (mt == 1) return launch_decode_t<T, 256, 1, 4, 3>(p, stream);
+  }
+  return cudaErrorInvalidValue;
+}
+
+bool decode_supported(int d, int rows) {
+  if (d == 64 || d == 128) return rows <= 32;
+  if (d == 256) return rows <= 16;
+  return false;
+}
+
+cudaError_t launch_decode(const KParams& p, bool is_bf16, cudaStream_t stream) {
+  int rows = p.seqlen_q * p.group;
+  int mt = rows <= 16 ? 1 : 2;
+  return is_bf16 ? launch_decode_d<__nv_bfloat16>(p, mt, stream) : launch_decode_d<__half>(p, mt, stream);
+}
+
+}  // namespace fa

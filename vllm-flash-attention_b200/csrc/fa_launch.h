@@ -1,0 +1,34 @@
+// fa_launch.h — host-side launch entry points of the kernels (one per .cu file).
+#pragma once
+#include <cuda_runtime.h>
+#include "fa_common.cuh"
+
+namespace fa {
+
+// fa_decode.cu — rows = seqlen_q*group packed rows must satisfy decode_supported(d, rows).
+bool decode_supported(int d, int rows);
+cudaError_t launch_decode(const KParams& p, bool is_bf16, cudaStream_t stream);
+
+// fa_tile.cu — feature-complete mma.sync tile kernel, d in {32,64,...,256}.
+bool tile_supported(int d);
+int tile_block_m(int d);
+cudaError_t launch_tile(const KParams& p, bool is_bf16, cudaStream_t stream);
+
+// fa_combine.cu — LSE merge of split partials into (o, lse).
+// part_dtype/out_dtype: 0 fp32, 1 bf16, 2 fp16.  Output row (b,h,q) is written to
+// o + [cu_q ? cu_q[b]*o_row_stride : b*o_batch_stride] + q*o_row_stride + h*o_head_stride.
+struct CombineParams {
+  const void* o_part; const float* lse_part; void* o; float* lse;
+  int n_splits; int b, h, sq, d;
+  int64_t o_batch_stride, o_row_stride, o_head_stride;
+  const int* cu_seqlens_q;
+  int part_dtype, out_dtype;
+};
+cudaError_t launch_combine(const CombineParams& c, cudaStream_t stream);
+
+// fa_prefill_tc5.cu — tcgen05/TMA/TMEM prefill kernel, d in {64,128}.
+bool tc5_supported(const KParams& p);
+cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k,
+                               cudaStream_t stream);
+
+}  // namespace fa
