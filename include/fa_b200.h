@@ -129,6 +129,12 @@ int fa_b200_fwd(FaFwdParams* p, void* stream);
 int fa_b200_varlen_fwd(FaFwdParams* p, void* stream);
 int fa_b200_fwd_kvcache(FaFwdParams* p, void* stream);
 
+/* Append the new K/V rows of a fwd_kvcache call into the (paged) cache at cache_seqlens[b]+i, with
+ * rotary embedding on K (and on q, written to p->workspace as (b,seqlen_q,h,d)) when rotary_cos/sin
+ * are set — the append half of the reference's fused path (flash_fwd_kernel.h:672-824).  The caller
+ * then runs fa_b200_fwd_kvcache with knew/vnew/rotary cleared, seqlen_knew kept, q = rotated q. */
+int fa_b200_append_kv(FaFwdParams* p, void* stream);
+
 /* Merge `n` partial results (o_part: (n,rows,d) fp32 or bf16/fp16, lse_part: (n,rows) fp32)
  * into o (rows,d) + lse (rows): lse = logsumexp_s lse_s, o = sum_s exp(lse_s-lse) o_s.
  * Same algebra as combine_attn_seqk_parallel (flash_fwd_kernel.h:1092-1250); used for the

@@ -1,0 +1,237 @@
+"""GPU: behaviour of the drop-in boundary — auto dispatch, out=, errors, determinism, combine,
+append-KV + rotary, full-size configs against the reference kernel."""
+import ctypes as C
+import math
+
+import pytest
+import torch
+
+import _util
+import attention_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(autouse=True)
+def _auto_kernel():
+    from vllm_flash_attn import vllm_flash_attn_2_cuda as ext
+    ext._force_kernel = 0
+    yield
+    ext._force_kernel = 0
+
+
+def _ext():
+    from vllm_flash_attn import vllm_flash_attn_2_cuda as ext
+    return ext
+
+
+def test_auto_dispatch_picks_expected_kernels():
+    import vllm_flash_attn as fa
+    dev, dt = "cuda", torch.bfloat16
+    q = torch.randn(2, 512, 8, 64, device=dev, dtype=dt); k = torch.randn_like(q); v = torch.randn_like(q)
+    fa.flash_attn_func(q, k, v)
+    assert _ext().last_call_info["kernel_used"] == 1          # tcgen05 prefill
+    q1 = torch.randn(4, 1, 32, 128, device=dev, dtype=dt)
+    kc = torch.randn(4, 1024, 8, 128, device=dev, dtype=dt); vc = torch.randn_like(kc)
+    fa.flash_attn_with_kvcache(q1, kc, vc, cache_seqlens=torch.full((4,), 1000, dtype=torch.int32, device=dev))
+    assert _ext().last_call_info["kernel_used"] == 3          # decode
+    q2 = torch.randn(1, 200, 4, 96, device=dev, dtype=dt); k2 = torch.randn_like(q2)
+    fa.flash_attn_func(q2, k2, k2)
+    assert _ext().last_call_info["kernel_used"] == 2          # tile kernel (d=96)
+
+
+def test_c1_full_and_out_argument():
+    import vllm_flash_attn as fa
+    torch.manual_seed(0)
+    q = torch.randn(2, 512, 8, 64, device="cuda", dtype=torch.bfloat16); k = torch.randn_like(q); v = torch.randn_like(q)
+    out_buf = torch.empty_like(q)
+    out = fa.flash_attn_func(q, k, v, out=out_buf)
+    assert out.data_ptr() == out_buf.data_ptr()
+    ref32, _ = orc.attention_ref(q, k, v)
+    pt, _ = orc.attention_ref(q, k, v, upcast=False, reorder_ops=True)
+    assert (out.float() - ref32.float()).abs().max() <= 2 * (pt.float() - ref32.float()).abs().max() + 1e-5
+    if _util.ref_lib() is not None:
+        rk, _ = _util.ref_kernel_fwd(q, k, v)
+        assert (out.float() - ref32.float()).abs().max() <= 2 * (rk.float() - ref32.float()).abs().max() + 1e-5
+
+
+def test_errors_raise_runtime_error():
+    import vllm_flash_attn as fa
+    q = torch.randn(1, 8, 4, 64, device="cuda", dtype=torch.float32)
+    with pytest.raises(RuntimeError, match="fp16 and bf16"):
+        fa.flash_attn_func(q, q, q)
+    q = q.half()
+    with pytest.raises(RuntimeError, match="must divide"):
+        fa.flash_attn_func(q, q[:, :, :3], q[:, :, :3])
+    with pytest.raises(RuntimeError, match="dropout"):
+        fa.flash_attn_func(q, q, q, dropout_p=0.1)
+    kc = torch.randn(6, 24, 4, 64, device="cuda", dtype=torch.float16)
+    bt = torch.zeros(1, 2, dtype=torch.int32, device="cuda")
+    with pytest.raises(RuntimeError, match="divisible by 16"):
+        fa.flash_attn_with_kvcache(q, kc, kc, cache_seqlens=torch.tensor([20], dtype=torch.int32, device="cuda"), block_table=bt)
+
+
+def test_head_dim_padding_and_packed_wrappers():
+    import vllm_flash_attn as fa
+    torch.manual_seed(1)
+    qkv = torch.randn(2, 100, 3, 4, 40, device="cuda", dtype=torch.float16)     # d=40 -> padded to 64? (d%32 rule)
+    with pytest.raises(RuntimeError):
+        fa.flash_attn_qkvpacked_func(qkv)          # reference build: headdim must be a multiple of 32
+    qkv = torch.randn(2, 100, 3, 4, 64, device="cuda", dtype=torch.float16)
+    o1 = fa.flash_attn_qkvpacked_func(qkv, causal=True)
+    o2 = fa.flash_attn_func(qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2], causal=True)
+    assert torch.equal(o1, o2)
+    o3 = fa.flash_attn_kvpacked_func(qkv[:, :, 0], qkv[:, :, 1:], causal=True)
+    assert torch.equal(o1, o3)
+
+
+@pytest.mark.parametrize("kind", ["prefill", "decode_split"])
+def test_bitwise_deterministic(kind):
+    """tests/test_flash_attn.py:2107-2173 (race condition test): repeated calls are bit-identical."""
+    import vllm_flash_attn as fa
+    torch.manual_seed(0)
+    dev, dt = "cuda", torch.bfloat16
+    if kind == "prefill":
+        q = torch.randn(2, 1000, 8, 128, device=dev, dtype=dt); k = torch.randn(2, 1000, 2, 128, device=dev, dtype=dt); v = torch.randn_like(k)
+        f = lambda: fa.flash_attn_func(q, k, v, causal=True, return_attn_probs=True)[:2]
+    else:
+        q = torch.randn(1, 1, 32, 128, device=dev, dtype=dt)
+        kc = torch.randn(1, 20000, 8, 128, device=dev, dtype=dt); vc = torch.randn_like(kc)
+        cs = torch.tensor([19999], dtype=torch.int32, device=dev)
+        f = lambda: fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=cs, return_softmax_lse=True)
+    o0, l0 = f()
+    for _ in range(30):
+        o, l = f()
+        assert torch.equal(o, o0) and torch.equal(l, l0)
+
+
+def test_combine_entry_point():
+    from vllm_flash_attn._cabi import lib, check
+    torch.manual_seed(0)
+    n, rows, d = 5, 37, 128
+    o_p = torch.randn(n, rows, d, device="cuda")
+    l_p = torch.randn(n, rows, device="cuda") * 3
+    l_p[2] = float("-inf")
+    l_p[:, 5] = float("-inf")
+    o = torch.empty(rows, d, device="cuda", dtype=torch.bfloat16); lse = torch.empty(rows, device="cuda")
+    check(lib.fa_b200_combine(o_p.data_ptr(), l_p.data_ptr(), o.data_ptr(), lse.data_ptr(), n, rows, d, 0, 1,
+                              torch.cuda.current_stream().cuda_stream))
+    oc, lc = orc.combine_ref(o_p.cpu(), l_p.cpu())
+    assert (o.float().cpu() - oc).abs().max() < 2e-2
+    assert torch.isinf(lse[5]) and lse[5] > 0 and (o[5] == 0).all()
+    fin = torch.isfinite(lc)
+    assert (lse.cpu()[fin] - lc[fin]).abs().max() < 1e-4
+
+
+@pytest.mark.parametrize("paged", [False, True])
+@pytest.mark.parametrize("interleaved", [True, False])
+@pytest.mark.parametrize("rotary_frac", [0.0, 0.5, 1.0])
+def test_append_kv_and_rotary(paged, interleaved, rotary_frac):
+    """tests/test_flash_attn.py:1944-2074: new k/v are appended at cache_seqlens (rotary applied),
+    cache contents are checked afterwards, output matches attention over the updated cache."""
+    import vllm_flash_attn as fa
+    torch.manual_seed(0)
+    dev, dt = "cuda", torch.float16
+    b, sq, sk, skn, h, hk, d = 2, 3, 160, 3, 4, 2, 64
+    q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
+    kn = torch.randn(b, skn, hk, d, device=dev, dtype=dt); vn = torch.randn_like(kn)
+    lens = torch.tensor([100, 37], dtype=torch.int32, device=dev)
+    bt = None
+    if paged:
+        nblk = (sk // 16) * b * 2
+        kc = torch.randn(nblk, 16, hk, d, device=dev, dtype=dt); vc = torch.randn_like(kc)
+        bt = torch.randperm(nblk, device=dev).to(torch.int32).view(b, -1)[:, :sk // 16].contiguous()
+        kfull, vfull = orc.gather_paged(kc, bt).clone(), orc.gather_paged(vc, bt).clone()
+    else:
+        kc = torch.randn(b, sk, hk, d, device=dev, dtype=dt); vc = torch.randn_like(kc)
+        kfull, vfull = kc.clone(), vc.clone()
+    rd = int(rotary_frac * d) // 16 * 16
+    cos = sin = None
+    q_ro, kn_ro = q, kn
+    if rd > 0:
+        ang = torch.rand(sk, rd // 2, device=dev) * 2 * math.pi
+        cos, sin = torch.cos(ang).to(dt), torch.sin(ang).to(dt)
+
+        def rot(x, pos):                     # x (b,s,h,d), pos (b,s)
+            c = cos.float()[pos].unsqueeze(2); s_ = sin.float()[pos].unsqueeze(2)
+            xr = x.float().clone()
+            if interleaved:
+                x0, x1 = xr[..., 0:rd:2], xr[..., 1:rd:2]
+                xr[..., 0:rd:2], xr[..., 1:rd:2] = x0 * c - x1 * s_, x0 * s_ + x1 * c
+            else:
+                x0, x1 = xr[..., :rd // 2].clone(), xr[..., rd // 2:rd].clone()
+                xr[..., :rd // 2], xr[..., rd // 2:rd] = x0 * c - x1 * s_, x0 * s_ + x1 * c
+            return xr.to(dt)
+        pos_k = lens.long().view(b, 1) + torch.arange(skn, device=dev).view(1, -1)
+        kn_ro = rot(kn, pos_k)
+        pos_q = lens.long().view(b, 1) + torch.arange(sq, device=dev).view(1, -1)   # causal: by position
+        q_ro = rot(q, pos_q)
+    for i in range(b):
+        L = int(lens[i])
+        kfull[i, L:L + skn] = kn_ro[i]; vfull[i, L:L + skn] = vn[i]
+    out = fa.flash_attn_with_kvcache(q, kc, vc, kn, vn, rotary_cos=cos, rotary_sin=sin, cache_seqlens=lens,
+                                     block_table=bt, causal=True, rotary_interleaved=interleaved)
+    kafter = orc.gather_paged(kc, bt) if paged else kc
+    vafter = orc.gather_paged(vc, bt) if paged else vc
+    assert torch.allclose(kafter.float(), kfull.float(), atol=2e-3, rtol=1e-3)
+    assert torch.equal(vafter, vfull)
+    S = kfull.shape[1]
+    kpm = torch.arange(S, device=dev).expand(b, S) < (lens + skn).view(-1, 1)
+    ref32, _ = orc.attention_ref(q_ro, kfull, vfull, None, kpm, causal=True)
+    pt, _ = orc.attention_ref(q_ro, kfull, vfull, None, kpm, causal=True, upcast=False, reorder_ops=True)
+    assert (out.float() - ref32.float()).abs().max() <= 3 * (pt.float() - ref32.float()).abs().max() + 1e-5
+
+
+def test_cache_batch_idx_and_seqlen_k_zero():
+    import vllm_flash_attn as fa
+    torch.manual_seed(0)
+    dev, dt = "cuda", torch.bfloat16
+    q = torch.randn(2, 1, 8, 128, device=dev, dtype=dt)
+    kc = torch.randn(5, 300, 2, 128, device=dev, dtype=dt); vc = torch.randn_like(kc)
+    idx = torch.tensor([3, 1], dtype=torch.int32, device=dev)
+    lens = torch.tensor([300, 123], dtype=torch.int32, device=dev)
+    out = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=lens, cache_batch_idx=idx)
+    kpm = torch.arange(300, device=dev).expand(2, 300) < lens.view(-1, 1)
+    ref32, _ = orc.attention_ref(q, kc[idx.long()], vc[idx.long()], None, kpm)
+    assert (out.float() - ref32.float()).abs().max() < 2e-2
+    o = fa.flash_attn_func(q, kc[:2, :0], vc[:2, :0])
+    assert (o == 0).all()
+
+
+@pytest.mark.parametrize("cfg", ["C2_varlen_prefill", "C3_paged_decode"])
+def test_full_size_configs_vs_reference_kernel(cfg):
+    """BASELINE.json configs at full size: our output vs the reference FA2 kernel built for sm_100
+    (size-independent check: both must agree within bf16 rounding of outputs of magnitude <~ 1)."""
+    if _util.ref_lib() is None:
+        pytest.skip("oracle/_ref not built")
+    import vllm_flash_attn as fa
+    torch.manual_seed(0)
+    dev, dt = "cuda", torch.bfloat16
+    if cfg == "C2_varlen_prefill":
+        lens = [8192, 4096, 2048, 1024, 512, 256, 128, 128]
+        cu = torch.tensor([0] + list(torch.tensor(lens).cumsum(0)), dtype=torch.int32, device=dev)
+        q = torch.randn(16384, 32, 128, device=dev, dtype=dt)
+        k = torch.randn(16384, 8, 128, device=dev, dtype=dt); v = torch.randn_like(k)
+        out, lse, _ = fa.flash_attn_varlen_func(q, k, v, cu, cu, 8192, 8192, causal=True, return_attn_probs=True)
+        assert _ext().last_call_info["kernel_used"] == 1
+        rk, rl = _util.ref_kernel_varlen(q, k, v, cu, cu, 8192, 8192, causal=True)
+        # spot-check the shortest sequence against the fp32 oracle too
+        s0 = int(cu[-2]); qs, ks, vs = q[s0:].unsqueeze(0), k[s0:].unsqueeze(0), v[s0:].unsqueeze(0)
+        ref32, _ = orc.attention_ref(qs, ks, vs, causal=True)
+        e_new = (out[s0:].float() - ref32[0].float()).abs().max(); e_rk = (rk[s0:].float() - ref32[0].float()).abs().max()
+        assert e_new <= 2 * e_rk + 1e-5
+    else:
+        b, ctx, page = 256, 4096, 16
+        nblk = b * (ctx // page) * 5 // 4
+        kc = torch.randn(nblk, page, 8, 128, device=dev, dtype=dt); vc = torch.randn_like(kc)
+        bt = torch.randperm(nblk, device=dev)[: b * ctx // page].to(torch.int32).view(b, -1).contiguous()
+        q = torch.randn(b, 1, 32, 128, device=dev, dtype=dt)
+        lens = torch.randint(2048, ctx + 1, (b,), device=dev).to(torch.int32)
+        out, lse = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=lens, block_table=bt, causal=True, return_softmax_lse=True)
+        assert _ext().last_call_info["kernel_used"] == 3
+        rk, rl = _util.ref_kernel_kvcache(q, kc, vc, lens, bt, causal=True)
+    assert not torch.isnan(out.float()).any()
+    assert (out.float() - rk.float()).abs().max() < 2e-2
+    n = min(lse.shape[-1], rl.shape[-1])
+    fin = torch.isfinite(rl[..., :n]) & (rl[..., :n] != 0)
+    assert (lse[..., :n][fin] - rl[..., :n][fin]).abs().max() < 2e-3

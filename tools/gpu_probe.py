@@ -1,0 +1,230 @@
+"""GPU bring-up probe (development tool, not part of the product or the test-suite).
+
+Runs a matrix of small cases through the public API with a pinned kernel family, each in its own
+subprocess with a timeout (a hung tcgen05 pipeline must not take the whole gpurun call down), and
+writes one JSON line per case to gpurun_out/probe.jsonl: max-abs error of our kernel and of the
+reference FA2 kernel (oracle/_ref) against the fp32 attention_ref oracle.
+
+  python tools/gpu_probe.py                # all cases
+  python tools/gpu_probe.py --case NAME    # one case, in-process
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+K_TC5, K_TILE, K_DEC = 1, 2, 3
+
+
+def C(name, kern, kind="dense", **kw):
+    d = dict(name=name, kern=kern, kind=kind, b=2, sq=256, sk=256, h=4, hk=4, d=128, dtype="bf16",
+             causal=False, window=(-1, -1), alibi=False, pmode="t", page=0, splits=0, seed=0)
+    d.update(kw)
+    return d
+
+
+CASES = []
+for pm in ("t", "s"):
+    sfx = "_P" + pm
+    CASES += [
+        C("tc5_d128_1tile" + sfx, K_TC5, b=1, h=1, hk=1, sq=128, sk=128, pmode=pm),
+        C("tc5_d128_256" + sfx, K_TC5, b=1, h=2, hk=2, sq=256, sk=256, pmode=pm),
+        C("tc5_d128_1k" + sfx, K_TC5, sq=1024, sk=1024, pmode=pm),
+        C("tc5_d64_c1" + sfx, K_TC5, b=2, h=8, hk=8, sq=512, sk=512, d=64, pmode=pm),
+        C("tc5_d128_causal" + sfx, K_TC5, sq=1024, sk=1024, causal=True, h=8, hk=2, pmode=pm),
+        C("tc5_d128_causal_ragged" + sfx, K_TC5, sq=333, sk=777, causal=True, pmode=pm),
+        C("tc5_d64_causal_fp16" + sfx, K_TC5, sq=500, sk=500, d=64, causal=True, dtype="fp16", pmode=pm),
+        C("tc5_d128_sq_gt_sk" + sfx, K_TC5, sq=600, sk=200, causal=True, pmode=pm),
+        C("tc5_d128_local" + sfx, K_TC5, sq=700, sk=900, window=(100, 30), pmode=pm),
+        C("tc5_d128_alibi" + sfx, K_TC5, sq=300, sk=300, causal=True, alibi=True, pmode=pm),
+        C("tc5_varlen_causal" + sfx, K_TC5, kind="varlen", b=5, sq=700, sk=700, h=8, hk=2, causal=True, pmode=pm),
+    ]
+CASES += [
+    C("tile_d128_dense", K_TILE), C("tile_d64_causal", K_TILE, d=64, causal=True, sq=300, sk=431),
+    C("tile_d32_fp16", K_TILE, d=32, dtype="fp16", sq=100, sk=231, h=6, hk=2),
+    C("tile_d96_local", K_TILE, d=96, window=(40, 10), sq=200, sk=300),
+    C("tile_d256_causal", K_TILE, d=256, causal=True, sq=130, sk=130, h=2, hk=1),
+    C("tile_d160_alibi", K_TILE, d=160, alibi=True, sq=77, sk=140),
+    C("tile_d192", K_TILE, d=192, sq=64, sk=200), C("tile_d224_causal", K_TILE, d=224, causal=True, sq=100, sk=100),
+    C("tile_varlen", K_TILE, kind="varlen", b=4, sq=200, sk=200, causal=True, h=8, hk=2),
+    C("tile_varlen_paged16", K_TILE, kind="varlen", b=3, sq=150, sk=300, causal=True, page=16, h=8, hk=2),
+    C("tile_split", K_TILE, b=1, h=2, hk=2, sq=64, sk=4000, d=64),
+    C("tile_kvcache_paged256", K_TILE, kind="kvcache", b=2, sq=40, sk=900, page=256, causal=True, h=6, hk=6),
+    C("dec_d128_paged16", K_DEC, kind="kvcache", b=4, sq=1, sk=1000, page=16, h=8, hk=2, causal=True),
+    C("dec_d128_split", K_DEC, kind="kvcache", b=1, sq=1, sk=9000, page=16, h=32, hk=8, causal=True),
+    C("dec_d128_split_forced", K_DEC, kind="kvcache", b=2, sq=1, sk=700, page=0, h=4, hk=4, splits=5),
+    C("dec_d64_mqa", K_DEC, kind="kvcache", b=3, sq=1, sk=555, d=64, h=16, hk=1, dtype="fp16"),
+    C("dec_d128_sq4_causal", K_DEC, kind="kvcache", b=2, sq=4, sk=300, h=8, hk=2, causal=True, page=16),
+    C("dec_d128_g8_sq3", K_DEC, kind="kvcache", b=2, sq=3, sk=300, h=8, hk=1, causal=True),
+    C("dec_d256", K_DEC, kind="kvcache", b=2, sq=1, sk=400, d=256, h=4, hk=2),
+    C("dec_alibi", K_DEC, kind="kvcache", b=2, sq=1, sk=300, h=4, hk=4, alibi=True, causal=True),
+    C("dec_local", K_DEC, kind="kvcache", b=2, sq=2, sk=500, h=4, hk=2, window=(64, 0)),
+    C("dec_varlen_paged", K_DEC, kind="varlen", b=6, sq=1, sk=800, page=16, h=8, hk=2, causal=True),
+]
+
+
+def run_case(spec):
+    import torch
+    import _util  # noqa: F401  (sys.path)
+    import attention_oracle as orc
+    os.environ["FA_B200_TC5_P"] = spec["pmode"]
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import vllm_flash_attn_2_cuda as ext
+    ext._force_kernel = spec["kern"]
+    dev = "cuda"
+    dt = torch.bfloat16 if spec["dtype"] == "bf16" else torch.float16
+    torch.manual_seed(spec["seed"])
+    b, sq, sk, h, hk, d = (spec[x] for x in ("b", "sq", "sk", "h", "hk", "d"))
+    causal, window = spec["causal"], tuple(spec["window"])
+    slopes = (torch.rand(b, h, device=dev) * 0.3) if spec["alibi"] else None
+    res = dict(name=spec["name"])
+    refk = _util.ref_lib() is not None and d in (64, 128)
+
+    def errs(out, ref32, out_pt, out_refk=None):
+        r = dict(err=(out.float() - ref32.float()).abs().max().item(),
+                 err_pt=(out_pt.float() - ref32.float()).abs().max().item(),
+                 nan=bool(torch.isnan(out.float()).any().item()))
+        if out_refk is not None:
+            r["err_refk"] = (out_refk.float() - ref32.float()).abs().max().item()
+            r["vs_refk"] = (out.float() - out_refk.float()).abs().max().item()
+        return r
+
+    if spec["kind"] == "dense":
+        q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
+        k = torch.randn(b, sk, hk, d, device=dev, dtype=dt)
+        v = torch.randn(b, sk, hk, d, device=dev, dtype=dt)
+        out, lse, _ = fa.flash_attn_func(q, k, v, causal=causal, window_size=window, alibi_slopes=slopes, return_attn_probs=True)
+        bias = orc.attn_bias_from_alibi_slopes(slopes, sq, sk, causal=causal) if slopes is not None else None
+        ref32, _ = orc.attention_ref(q, k, v, attn_bias=bias, causal=causal, window_size=window)
+        out_pt, _ = orc.attention_ref(q, k, v, attn_bias=bias, causal=causal, window_size=window, upcast=False, reorder_ops=True)
+        lref = orc.lse_ref(q, k, attn_bias=bias, causal=causal, window_size=window)
+        ork = _util.ref_kernel_fwd(q, k, v, causal, window, slopes)[0] if refk else None
+        res.update(errs(out, ref32, out_pt, ork))
+        fin = torch.isfinite(lref)
+        res["lse_err"] = (lse[fin] - lref[fin]).abs().max().item() if fin.any() else 0.0
+        res["lse_inf_ok"] = bool((torch.isinf(lse) == torch.isinf(lref)).all().item())
+    elif spec["kind"] == "varlen":
+        g = torch.Generator(device="cpu").manual_seed(spec["seed"])
+        if sq == 1:
+            lens_q = torch.ones(b, dtype=torch.int64)
+        else:
+            lens_q = torch.randint(max(1, sq // 3), sq + 1, (b,), generator=g)
+        lens_k = lens_q.clone() if (sq == sk and sq > 1) else torch.randint(max(1, sk // 3), sk + 1, (b,), generator=g)
+        cu_q = torch.zeros(b + 1, dtype=torch.int32); cu_q[1:] = lens_q.cumsum(0)
+        cu_k = torch.zeros(b + 1, dtype=torch.int32); cu_k[1:] = lens_k.cumsum(0)
+        q = torch.randn(int(cu_q[-1]), h, d, device=dev, dtype=dt)
+        kd = torch.randn(int(cu_k[-1]), hk, d, device=dev, dtype=dt)
+        vd = torch.randn(int(cu_k[-1]), hk, d, device=dev, dtype=dt)
+        max_q, max_k = int(lens_q.max()), int(lens_k.max())
+        bt = None
+        kk, vv = kd, vd
+        if spec["page"]:
+            page = spec["page"]
+            nb_seq = (max_k + page - 1) // page
+            nblocks = nb_seq * b * 3
+            kk = torch.randn(nblocks, page, hk, d, device=dev, dtype=dt)
+            vv = torch.randn(nblocks, page, hk, d, device=dev, dtype=dt)
+            bt = torch.randperm(nblocks, generator=g).to(torch.int32).view(b, -1).to(dev)
+            kg, vg = orc.gather_paged(kk, bt), orc.gather_paged(vv, bt)
+            kd = torch.cat([kg[i, :int(lens_k[i])] for i in range(b)])
+            vd = torch.cat([vg[i, :int(lens_k[i])] for i in range(b)])
+        cq, ck = cu_q.to(dev), cu_k.to(dev)
+        out, lse, _ = fa.flash_attn_varlen_func(q, kk, vv, cq, ck, max_q, max_k, causal=causal, window_size=window,
+                                                 alibi_slopes=slopes, return_attn_probs=True, block_table=bt)
+        ref32, lref = orc.attention_ref_varlen(q, kd, vd, cu_q, cu_k, causal=causal, window_size=window, alibi_slopes=slopes)
+        out_pt, _ = orc.attention_ref_varlen(q, kd, vd, cu_q, cu_k, causal=causal, window_size=window, alibi_slopes=slopes,
+                                             upcast=False, reorder_ops=True)
+        ork = None
+        if refk and slopes is None:
+            ork = _util.ref_kernel_varlen(q, kk, vv, cq, ck, max_q, max_k, causal, window, bt)[0]
+        res.update(errs(out, ref32, out_pt, ork))
+        lerr = 0.0
+        for i in range(b):
+            n = int(lens_q[i])
+            a, r_ = lse[i, :, :n].cpu(), lref[i, :, :n]
+            fin = torch.isfinite(r_)
+            if fin.any():
+                lerr = max(lerr, (a[fin] - r_[fin]).abs().max().item())
+        res["lse_err"] = lerr
+    else:  # kvcache
+        g = torch.Generator(device="cpu").manual_seed(spec["seed"])
+        q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
+        lens = torch.randint(max(sq, sk // 2), sk + 1, (b,), generator=g).to(torch.int32)
+        lens[0] = sk
+        bt = None
+        if spec["page"]:
+            page = spec["page"]
+            nb_seq = (sk + page - 1) // page
+            nblocks = nb_seq * b * 3
+            kc = torch.randn(nblocks, page, hk, d, device=dev, dtype=dt)
+            vc = torch.randn(nblocks, page, hk, d, device=dev, dtype=dt)
+            bt = torch.randperm(nblocks, generator=g).to(torch.int32).view(b, -1)[:, :nb_seq].contiguous().to(dev)
+            kfull, vfull = orc.gather_paged(kc, bt), orc.gather_paged(vc, bt)
+        else:
+            kc = torch.randn(b, sk, hk, d, device=dev, dtype=dt)
+            vc = torch.randn(b, sk, hk, d, device=dev, dtype=dt)
+            kfull, vfull = kc, vc
+        lens_d = lens.to(dev)
+        out, lse = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=lens_d, block_table=bt, causal=causal,
+                                              window_size=window, alibi_slopes=slopes, num_splits=spec["splits"],
+                                              return_softmax_lse=True)
+        S = kfull.shape[1]
+        kpm = torch.arange(S, device=dev).expand(b, S) < lens_d.view(-1, 1)
+        bias = None
+        if slopes is not None:
+            bias = orc.attn_bias_from_alibi_slopes(slopes, sq, S, None, kpm, causal=causal)
+        ref32, _ = orc.attention_ref(q, kfull, vfull, None, kpm, bias, causal=causal, window_size=window)
+        out_pt, _ = orc.attention_ref(q, kfull, vfull, None, kpm, bias, causal=causal, window_size=window,
+                                      upcast=False, reorder_ops=True)
+        lref = orc.lse_ref(q, kfull, kpm, None, bias, causal=causal, window_size=window)
+        ork = None
+        if refk and slopes is None:
+            ork = _util.ref_kernel_kvcache(q, kc, vc, lens_d, bt, causal, window, spec["splits"])[0]
+        res.update(errs(out, ref32, out_pt, ork))
+        fin = torch.isfinite(lref)
+        res["lse_err"] = (lse[fin] - lref[fin]).abs().max().item()
+    res.update(ext.last_call_info)
+    torch.cuda.synchronize()
+    res["ok"] = bool((not res["nan"]) and res["err"] <= 2 * res["err_pt"] + 1e-4 and res["lse_err"] < 2e-3)
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--case")
+    ap.add_argument("--filter", default="")
+    ap.add_argument("--timeout", type=int, default=150)
+    a = ap.parse_args()
+    if a.case:
+        spec = next(c for c in CASES if c["name"] == a.case)
+        print("RESULT " + json.dumps(run_case(spec)))
+        return
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    outp = open(os.path.join(ROOT, "gpurun_out", "probe.jsonl"), "a")
+    nfail = 0
+    for spec in CASES:
+        if a.filter and a.filter not in spec["name"]:
+            continue
+        t0 = time.time()
+        try:
+            pr = subprocess.run([sys.executable, __file__, "--case", spec["name"]], capture_output=True, text=True,
+                                timeout=a.timeout)
+            line = next((l for l in pr.stdout.splitlines() if l.startswith("RESULT ")), None)
+            res = json.loads(line[7:]) if line else dict(name=spec["name"], ok=False, rc=pr.returncode,
+                                                         stderr=pr.stderr[-1500:])
+        except subprocess.TimeoutExpired:
+            res = dict(name=spec["name"], ok=False, timeout=True)
+        res["secs"] = round(time.time() - t0, 1)
+        nfail += 0 if res.get("ok") else 1
+        outp.write(json.dumps(res) + "\n"); outp.flush()
+        print(json.dumps(res), flush=True)
+    print(f"probe done: {nfail} failing")
+
+
+if __name__ == "__main__":
+    main()

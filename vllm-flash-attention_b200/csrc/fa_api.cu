@@ -1,0 +1,299 @@
+// fa_api.cu — the C ABI of libfa_b200.so (include/fa_b200.h): argument validation, the
+// reference's parameter normalisation, kernel choice, split-KV heuristic and launches.
+// This file is the B200-native replacement of the reference's host glue
+// (csrc/flash_attn/flash_api.cpp:21-937) minus everything that needs torch (allocation and
+// tensor unwrapping live in the Python shim, vllm_flash_attn/_cabi.py).
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+#include "fa_b200.h"
+#include "fa_launch.h"
+
+using namespace fa;
+
+static thread_local char g_err[768] = "";
+static int fail(int code, const char* fmt, ...) {
+  va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap);
+  return code;
+}
+#define FA_CHECK(cond, ...) do { if (!(cond)) return fail(FA_ERR_INVALID, __VA_ARGS__); } while (0)
+
+extern "C" int fa_b200_abi_version(void) { return FA_B200_ABI_VERSION; }
+extern "C" size_t fa_b200_params_size(void) { return sizeof(FaFwdParams); }
+extern "C" const char* fa_b200_last_error(void) { return g_err; }
+
+// Wave-efficiency split choice — the rule of num_splits_heuristic (flash_api.cpp:158-192):
+// 1 split if the grid nearly fills the SMs; otherwise the smallest eligible split count whose
+// wave efficiency is within 85 % of the best.
+extern "C" int fa_b200_num_splits_heuristic(int work, int num_sms, int num_n_blocks, int max_splits) {
+  if (work >= 0.8f * num_sms) return 1;
+  max_splits = std::min(std::min(max_splits, num_sms), num_n_blocks);
+  if (max_splits < 1) return 1;
+  auto cdiv = [](int a, int b) { return (a + b - 1) / b; };
+  auto eligible = [&](int s) { return s == 1 || cdiv(num_n_blocks, s) != cdiv(num_n_blocks, s - 1); };
+  std::vector<float> eff(max_splits + 1, 0.f);
+  float best = 0.f;
+  for (int s = 1; s <= max_splits; s++) {
+    if (!eligible(s)) continue;
+    float waves = float(work * s) / num_sms;
+    eff[s] = waves / std::ceil(waves);
+    best = std::max(best, eff[s]);
+  }
+  for (int s = 1; s <= max_splits; s++)
+    if (eligible(s) && eff[s] >= 0.85f * best) return s;
+  return 1;
+}
+
+static int device_sms() {
+  static int sms[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (!sms[dev]) { int v = 0; cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev); sms[dev] = v > 0 ? v : 148; }
+  return sms[dev];
+}
+
+enum Op { OP_FWD = 0, OP_VARLEN = 1, OP_KVCACHE = 2 };
+
+struct Plan {
+  KParams k;
+  int kernel;      // FA_KERNEL_*
+  int num_splits;
+  size_t ws_bytes;
+  bool is_bf16;
+};
+
+// Validation + normalisation shared by the three ops.  Mirrors the checks of mha_fwd /
+// mha_varlen_fwd / mha_fwd_kvcache that do not need tensor metadata beyond what FaFwdParams holds.
+static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
+  FA_CHECK(a != nullptr, "params is NULL");
+  FA_CHECK(a->q && a->k && a->v && a->o, "q, k, v, out must be non-NULL device pointers");
+  FA_CHECK(a->b > 0, "batch size must be positive");                                   // flash_api.cpp:284
+  FA_CHECK(a->d > 0 && a->d <= 256, "FlashAttention forward only supports head dimension at most 256");  // :286
+  FA_CHECK(a->d % 8 == 0, "head dimension must be a multiple of 8 (pad in the caller, flash_api.cpp:310-319)");
+  FA_CHECK(a->h > 0 && a->h_k > 0 && a->h % a->h_k == 0,
+           "Number of heads in key/value must divide number of heads in query");       // :287
+  FA_CHECK(a->seqlen_q >= 0 && a->seqlen_k >= 0, "negative sequence length");
+  FA_CHECK(a->is_bf16 == 0 || a->is_bf16 == 1, "FlashAttention only support fp16 and bf16 data type");  // :262
+  if (op == OP_VARLEN) FA_CHECK(a->cu_seqlens_q && a->cu_seqlens_k, "cu_seqlens_q/k must be given for varlen_fwd");
+  if (op != OP_VARLEN) FA_CHECK(a->cu_seqlens_q == nullptr, "cu_seqlens_q is only valid for varlen_fwd");
+  const bool paged = a->block_table != nullptr;
+  if (paged) {
+    FA_CHECK(op != OP_FWD, "block_table is not supported by fwd");
+    FA_CHECK(a->page_block_size > 0 && a->page_block_size % 16 == 0,
+             "Paged KV cache block size must be divisible by 16");                     // :491,:735
+    FA_CHECK(a->cache_batch_idx == nullptr, "Paged KVcache does not support cache_batch_idx");  // :718
+    FA_CHECK(a->max_blocks_per_seq > 0, "block_table must have at least one column");
+  }
+  if (a->alibi_slopes == nullptr) FA_CHECK(a->alibi_slopes_batch_stride == 0, "alibi stride without slopes");
+  FA_CHECK(a->knew == nullptr && a->vnew == nullptr && a->rotary_cos == nullptr,
+           "append-KV / rotary are applied by fa_b200_append_kv before the attention call");
+  FA_CHECK(a->seqlen_knew >= 0 && (a->seqlen_knew == 0 || op == OP_KVCACHE), "seqlen_knew is only valid for fwd_kvcache");
+
+  KParams& k = pl->k;
+  memset(&k, 0, sizeof k);
+  k.q = a->q; k.k = a->k; k.v = a->v; k.o = a->o; k.lse = a->softmax_lse;
+  k.q_batch_stride = a->q_batch_stride; k.q_row_stride = a->q_row_stride; k.q_head_stride = a->q_head_stride;
+  k.k_batch_stride = a->k_batch_stride; k.k_row_stride = a->k_row_stride; k.k_head_stride = a->k_head_stride;
+  k.v_batch_stride = a->v_batch_stride; k.v_row_stride = a->v_row_stride; k.v_head_stride = a->v_head_stride;
+  k.o_batch_stride = a->o_batch_stride; k.o_row_stride = a->o_row_stride; k.o_head_stride = a->o_head_stride;
+  k.b = a->b; k.seqlen_q = a->seqlen_q; k.seqlen_k = a->seqlen_k; k.h = a->h; k.h_k = a->h_k; k.d = a->d;
+  k.group = a->h / a->h_k;
+  k.scale = a->softmax_scale; k.scale_log2 = a->softmax_scale * 1.4426950408889634f;
+  k.alibi_slopes = a->alibi_slopes; k.alibi_batch_stride = a->alibi_slopes_batch_stride;
+  k.cu_seqlens_q = a->cu_seqlens_q; k.cu_seqlens_k = a->cu_seqlens_k; k.seqused_k = a->seqused_k;
+  k.is_seqlens_k_cumulative = op == OP_KVCACHE ? 0 : 1;
+  if (op == OP_KVCACHE && a->cu_seqlens_k == nullptr) k.is_seqlens_k_cumulative = 1;
+  k.block_table = a->block_table; k.block_table_batch_stride = a->block_table_batch_stride;
+  k.page_block_size = a->page_block_size; k.max_blocks_per_seq = a->max_blocks_per_seq; k.num_blocks = a->num_blocks;
+  k.cache_batch_idx = a->cache_batch_idx;
+  k.seqlen_knew = a->seqlen_knew;   // rows already appended by fa_b200_append_kv
+  k.lse_seq_stride = a->seqlen_q;
+
+  // ---- mask normalisation (flash_api.cpp:289-294 and set_params_fprop :119-126) ----
+  int wl = a->window_left, wr = a->window_right;
+  bool causal = a->is_causal != 0;
+  if (wl >= a->seqlen_k) wl = -1;
+  if (wr >= a->seqlen_k) wr = -1;
+  if (a->seqlen_q == 1 && !a->alibi_slopes) causal = false;   // :293,:493,:744
+  if (causal) wr = 0;
+  k.is_causal = wl < 0 && wr == 0;
+  if (wl < 0 && wr >= 0) wl = a->seqlen_k;
+  if (wl >= 0 && wr < 0) wr = a->seqlen_k;
+  k.window_left = wl; k.window_right = wr;
+  k.is_local = (wl >= 0 || wr >= 0) && !k.is_causal;
+
+  pl->is_bf16 = a->is_bf16 != 0;
+  const int num_sms = a->num_sms > 0 ? a->num_sms : device_sms();
+
+  // ---- kernel choice ----
+  const int rows = a->seqlen_q * k.group;     // packed rows per (sequence, kv head)
+  int kernel = a->force_kernel;
+  k.num_splits = 1;
+  if (kernel == FA_KERNEL_NONE) {
+    if (decode_supported(a->d, rows)) kernel = FA_KERNEL_DECODE;
+    else if (tc5_supported(k)) kernel = FA_KERNEL_TC5_PREFILL;
+    else kernel = FA_KERNEL_TILE;
+  }
+  if (kernel == FA_KERNEL_DECODE) FA_CHECK(decode_supported(a->d, rows), "decode kernel: d/rows not supported");
+  if (kernel == FA_KERNEL_TC5_PREFILL) FA_CHECK(tc5_supported(k), "tcgen05 prefill kernel: shape/layout not supported");
+  if (kernel == FA_KERNEL_TILE) FA_CHECK(tile_supported(a->d), "head dimension must be a multiple of 32 (reference build: -DFLASHATTENTION_DISABLE_UNEVEN_K)");
+  pl->kernel = kernel;
+
+  // ---- split-KV choice ----
+  // The reference consults its heuristic in mha_fwd (:375-377), in varlen only for GQA-packed
+  // decode (:618-623) and in kvcache with the caller's num_splits (:903-905).  We split only in
+  // the two kernels that write partials, sized for 2 resident CTAs per SM.
+  int splits = 1;
+  const bool may_split = kernel != FA_KERNEL_TC5_PREFILL &&
+                         (op == OP_KVCACHE || op == OP_FWD || (op == OP_VARLEN && a->seqlen_q == 1));
+  if (may_split && a->seqlen_k > 0) {
+    const int req = op == OP_KVCACHE ? a->num_splits : 0;
+    if (req >= 1) splits = req;
+    else {
+      const int blk = kernel == FA_KERNEL_DECODE ? 256 : 128;   // keys per unit of split work
+      const int n_blocks = (a->seqlen_k + blk - 1) / blk;
+      const int work = kernel == FA_KERNEL_DECODE ? a->b * a->h_k
+                                                  : a->b * a->h * ((a->seqlen_q + 63) / 64);
+      splits = fa_b200_num_splits_heuristic(work, num_sms * 2, n_blocks, 128);
+    }
+    FA_CHECK(splits <= 128, "num_splits > 128 not supported");                         // :217
+  }
+  k.num_splits = pl->num_splits = splits;
+  pl->ws_bytes = splits > 1 ? (size_t)splits * a->b * a->h * std::max(a->seqlen_q, 1) * (a->d + 1) * sizeof(float) : 0;
+  return FA_OK;
+}
+
+static int run_plan(FaFwdParams* a, int op, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  g_err[0] = 0;
+  Plan pl;
+  int rc = make_plan(a, op, &pl);
+  if (rc != FA_OK) return rc;
+  a->kernel_used = pl.kernel; a->num_splits = pl.num_splits; a->launches = 0;
+  KParams& k = pl.k;
+  if (a->seqlen_q == 0 || a->b == 0) return FA_OK;
+  if (pl.num_splits > 1) {
+    if (a->workspace == nullptr || a->workspace_bytes < pl.ws_bytes)
+      return fail(FA_ERR_WORKSPACE, "split-KV workspace too small: need %zu bytes, got %zu", pl.ws_bytes, a->workspace_bytes);
+    const size_t rows = (size_t)a->b * a->h * a->seqlen_q;
+    k.lse_accum = reinterpret_cast<float*>(a->workspace);
+    k.o_accum = k.lse_accum + (size_t)pl.num_splits * rows;
+    if ((reinterpret_cast<uintptr_t>(k.o_accum) & 15) != 0)   // keep float4 alignment
+      k.o_accum = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(k.o_accum) + 15) & ~(uintptr_t)15);
+  }
+  cudaError_t e = cudaSuccess;
+  switch (pl.kernel) {
+    case FA_KERNEL_DECODE: e = launch_decode(k, pl.is_bf16, stream); break;
+    case FA_KERNEL_TILE: e = launch_tile(k, pl.is_bf16, stream); break;
+    case FA_KERNEL_TC5_PREFILL: e = launch_prefill_tc5(k, pl.is_bf16, a->total_q, a->total_k, stream); break;
+    default: return fail(FA_ERR_INVALID, "unknown kernel id %d", pl.kernel);
+  }
+  if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in attention kernel launch: %s", cudaGetErrorString(e));
+  a->launches = 1;
+  if (pl.num_splits > 1) {
+    CombineParams c;
+    c.o_part = k.o_accum; c.lse_part = k.lse_accum; c.o = a->o; c.lse = a->softmax_lse;
+    c.n_splits = pl.num_splits; c.b = a->b; c.h = a->h; c.sq = a->seqlen_q; c.d = a->d;
+    c.o_batch_stride = a->o_batch_stride; c.o_row_stride = a->o_row_stride; c.o_head_stride = a->o_head_stride;
+    c.cu_seqlens_q = a->cu_seqlens_q; c.part_dtype = 0; c.out_dtype = pl.is_bf16 ? 1 : 2;
+    e = launch_combine(c, stream);
+    if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in combine kernel launch: %s", cudaGetErrorString(e));
+    a->launches = 2;
+  }
+  return FA_OK;
+}
+
+extern "C" size_t fa_b200_workspace_bytes(const FaFwdParams* p, int op) {
+  Plan pl;
+  if (op < 0 || op > 2 || make_plan(p, op, &pl) != FA_OK) return (size_t)-1;
+  return pl.ws_bytes ? pl.ws_bytes + 16 : 0;
+}
+
+// mha_fwd (flash_api.cpp:240-420): dense (b,s,h,d) tensors.
+extern "C" int fa_b200_fwd(FaFwdParams* p, void* stream) {
+  if (p && (p->block_table || p->cache_batch_idx || p->cu_seqlens_k || p->seqused_k))
+    return fail(FA_ERR_INVALID, "fwd takes dense tensors only (no block_table / cache_batch_idx / seqlens)");
+  return run_plan(p, OP_FWD, stream);
+}
+
+// mha_varlen_fwd (flash_api.cpp:422-669): packed (total,h,d) q with cu_seqlens; k/v packed or paged.
+extern "C" int fa_b200_varlen_fwd(FaFwdParams* p, void* stream) {
+  if (p && p->cache_batch_idx) return fail(FA_ERR_INVALID, "varlen_fwd does not take cache_batch_idx");
+  return run_plan(p, OP_VARLEN, stream);
+}
+
+// mha_fwd_kvcache (flash_api.cpp:671-937): q (b,sq,h,d) against a (paged) cache with per-sequence
+// lengths in cu_seqlens_k (not cumulative, :859-867).
+extern "C" int fa_b200_fwd_kvcache(FaFwdParams* p, void* stream) {
+  return run_plan(p, OP_KVCACHE, stream);
+}
+
+extern "C" int fa_b200_combine(const void* o_part, const float* lse_part, void* o, float* lse, int32_t n,
+                               int64_t rows, int32_t d, int32_t part_dtype, int32_t out_dtype, void* stream) {
+  g_err[0] = 0;
+  if (!o_part || !lse_part || !o) return fail(FA_ERR_INVALID, "combine: NULL pointer");
+  if (n < 1 || n > 128) return fail(FA_ERR_INVALID, "combine: n must be in [1,128]");
+  if (d % 4 != 0 || d <= 0) return fail(FA_ERR_INVALID, "combine: d must be a positive multiple of 4");
+  if (rows > 0x7fffffff) return fail(FA_ERR_INVALID, "combine: too many rows");
+  CombineParams c;
+  c.o_part = o_part; c.lse_part = lse_part; c.o = o; c.lse = lse;
+  c.n_splits = n; c.b = 1; c.h = 1; c.sq = (int)rows; c.d = d;
+  c.o_batch_stride = 0; c.o_row_stride = d; c.o_head_stride = 0; c.cu_seqlens_q = nullptr;
+  c.part_dtype = part_dtype; c.out_dtype = out_dtype;
+  cudaError_t e = launch_combine(c, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in combine kernel launch: %s", cudaGetErrorString(e));
+  return FA_OK;
+}
+
+// Append (and rotate) the new K/V rows of a fwd_kvcache call — the first half of the reference's
+// fused append path (flash_fwd_kernel.h:672-824).  Takes the same parameter block as
+// fa_b200_fwd_kvcache with knew/vnew (and optionally rotary_cos/sin) set; if rotary is given,
+// `workspace` must hold b*seqlen_q*h*d elements and receives the rotated q, which the caller then
+// passes as q to fa_b200_fwd_kvcache together with seqlen_knew.
+extern "C" int fa_b200_append_kv(FaFwdParams* a, void* stream) {
+  g_err[0] = 0;
+  FA_CHECK(a && a->knew && a->vnew, "append_kv: knew and vnew must be given");
+  FA_CHECK(a->cu_seqlens_k != nullptr, "seqlens_k must be passed if key/value are passed");
+  FA_CHECK(a->seqlen_knew > 0, "append_kv: seqlen_knew must be positive");
+  FA_CHECK(a->d % 8 == 0, "append_kv: head dimension must be a multiple of 8");
+  const bool rotary = a->rotary_cos != nullptr;
+  if (rotary) {
+    FA_CHECK(a->rotary_sin != nullptr, "If rotary cos is provided, rotary sin must also be provided");
+    FA_CHECK(a->rotary_dim <= a->d, "rotary_dim must be <= headdim");
+    FA_CHECK(a->rotary_dim % 16 == 0, "Only rotary dimensions divisible by 16 are currently supported");
+    FA_CHECK(a->workspace && a->workspace_bytes >= (size_t)a->b * a->seqlen_q * a->h * a->d * 2,
+             "append_kv: workspace for the rotated q is too small");
+  }
+  if (a->block_table) FA_CHECK(a->page_block_size > 0 && a->page_block_size % 16 == 0, "Paged KV cache block size must be divisible by 16");
+  // same mask normalisation as the attention call decides whether q rows rotate by position
+  int wl = a->window_left, wr = a->window_right;
+  bool causal = a->is_causal != 0;
+  if (wl >= a->seqlen_k) wl = -1;
+  if (wr >= a->seqlen_k) wr = -1;
+  if (a->seqlen_q == 1 && !a->alibi_slopes) causal = false;
+  if (causal) wr = 0;
+  AppendParams p;
+  memset(&p, 0, sizeof p);
+  p.knew = a->knew; p.vnew = a->vnew; p.kcache = const_cast<void*>(a->k); p.vcache = const_cast<void*>(a->v);
+  p.q = a->q; p.q_rot = rotary ? a->workspace : nullptr;
+  p.knew_batch_stride = a->knew_batch_stride; p.knew_row_stride = a->knew_row_stride; p.knew_head_stride = a->knew_head_stride;
+  p.vnew_batch_stride = a->vnew_batch_stride; p.vnew_row_stride = a->vnew_row_stride; p.vnew_head_stride = a->vnew_head_stride;
+  p.k_batch_stride = a->k_batch_stride; p.k_row_stride = a->k_row_stride; p.k_head_stride = a->k_head_stride;
+  p.v_batch_stride = a->v_batch_stride; p.v_row_stride = a->v_row_stride; p.v_head_stride = a->v_head_stride;
+  p.q_batch_stride = a->q_batch_stride; p.q_row_stride = a->q_row_stride; p.q_head_stride = a->q_head_stride;
+  p.b = a->b; p.h = a->h; p.h_k = a->h_k; p.d = a->d; p.seqlen_q = a->seqlen_q; p.seqlen_k = a->seqlen_k;
+  p.seqlen_knew = a->seqlen_knew;
+  p.cache_seqlens = a->cu_seqlens_k; p.cache_batch_idx = a->cache_batch_idx;
+  p.block_table = a->block_table; p.block_table_batch_stride = a->block_table_batch_stride;
+  p.page_block_size = a->page_block_size; p.max_blocks_per_seq = a->max_blocks_per_seq;
+  p.rotary_cos = a->rotary_cos; p.rotary_sin = a->rotary_sin;
+  p.rotary_dim = rotary ? a->rotary_dim : 0; p.seqlen_ro = a->seqlen_ro; p.is_rotary_interleaved = a->is_rotary_interleaved;
+  p.rot_by_qpos = (wr >= 0 || wl >= 0) ? 1 : 0;   // causal or local after normalisation
+  cudaError_t e = launch_append(p, a->is_bf16 != 0, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in append kernel launch: %s", cudaGetErrorString(e));
+  return FA_OK;
+}

@@ -1,0 +1,140 @@
+// fa_append.cu — append new K/V rows into the (paged) KV cache, with rotary embedding on K and Q.
+//
+// The reference fuses this into the split-KV attention kernel (src/flash_fwd_kernel.h:672-824,
+// src/rotary.h:19-145): new rows are written at positions cache_seqlens[b] + i, K is rotated with
+// cos/sin taken at its position, Q with cos/sin at cache_seqlens[b] + (causal|local ? qpos : 0).
+// Here it is a separate, tiny, purely bandwidth-bound kernel that runs before the attention
+// kernel on the same stream (the attention kernel then sees seqlen = cache_seqlens + seqlen_knew),
+// which also removes the benign GQA write race the reference documents (:678-680).
+// Rotation is done in fp32 and rounded once, like the reference.
+#include "fa_common.cuh"
+#include "fa_launch.h"
+
+namespace fa {
+
+template <typename T> __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]);
+template <> __device__ __forceinline__ void unpack8<__nv_bfloat16>(const uint4& u, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; i++) { f[2 * i] = __low2float(h[i]); f[2 * i + 1] = __high2float(h[i]); }
+}
+template <> __device__ __forceinline__ void unpack8<__half>(const uint4& u, float (&f)[8]) {
+  const __half2* h = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; i++) { f[2 * i] = __low2float(h[i]); f[2 * i + 1] = __high2float(h[i]); }
+}
+template <typename T> __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+  uint4 u;
+  u.x = Pack2<T>::pack(f[0], f[1]); u.y = Pack2<T>::pack(f[2], f[3]);
+  u.z = Pack2<T>::pack(f[4], f[5]); u.w = Pack2<T>::pack(f[6], f[7]);
+  return u;
+}
+
+// Copy one row of d elements src -> dst, rotating the first rotary_dim elements.
+// Called by `nthreads` consecutive threads (tid in [0,nthreads)).
+template <typename T>
+__device__ __forceinline__ void rotate_row(const T* src, T* dst, int d, int rotary_dim, bool interleaved,
+                                           const T* cosr, const T* sinr, int tid, int nthreads) {
+  const int nchunks = d / 8, rot_chunks = rotary_dim / 8;
+  if (interleaved || rotary_dim == 0) {
+    for (int c = tid; c < nchunks; c += nthreads) {
+      uint4 u = *reinterpret_cast<const uint4*>(src + c * 8);
+      if (c < rot_chunks) {
+        float x[8], cs[8], sn[8];   // only the first 4 of cs / sn are used
+        unpack8<T>(u, x);
+        // pairs (2j, 2j+1) use cos/sin[c*4 + j]  (rotary.h:19-78)
+        uint2 cu = *reinterpret_cast<const uint2*>(cosr + c * 4), su = *reinterpret_cast<const uint2*>(sinr + c * 4);
+        uint4 c4 = make_uint4(cu.x, cu.y, 0, 0), s4 = make_uint4(su.x, su.y, 0, 0);
+        unpack8<T>(c4, cs); unpack8<T>(s4, sn);
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          float a = x[2 * j], b = x[2 * j + 1];
+          x[2 * j] = a * cs[j] - b * sn[j];
+          x[2 * j + 1] = a * sn[j] + b * cs[j];
+        }
+        u = pack8<T>(x);
+      }
+      *reinterpret_cast<uint4*>(dst + c * 8) = u;
+    }
+  } else {
+    // contiguous (NeoX): pairs (j, j + rotary_dim/2) use cos/sin[j]  (rotary.h:82-145)
+    const int half_chunks = rot_chunks / 2;
+    for (int c = tid; c < nchunks - half_chunks; c += nthreads) {
+      if (c < half_chunks) {
+        uint4 u0 = *reinterpret_cast<const uint4*>(src + c * 8);
+        uint4 u1 = *reinterpret_cast<const uint4*>(src + (c + half_chunks) * 8);
+        uint4 cu = *reinterpret_cast<const uint4*>(cosr + c * 8), su = *reinterpret_cast<const uint4*>(sinr + c * 8);
+        float x0[8], x1[8], cs[8], sn[8];
+        unpack8<T>(u0, x0); unpack8<T>(u1, x1); unpack8<T>(cu, cs); unpack8<T>(su, sn);
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          float a = x0[j], b = x1[j];
+          x0[j] = a * cs[j] - b * sn[j];
+          x1[j] = a * sn[j] + b * cs[j];
+        }
+        *reinterpret_cast<uint4*>(dst + c * 8) = pack8<T>(x0);
+        *reinterpret_cast<uint4*>(dst + (c + half_chunks) * 8) = pack8<T>(x1);
+      } else {
+        const int cc = c + half_chunks;   // chunks beyond the rotary part
+        *reinterpret_cast<uint4*>(dst + cc * 8) = *reinterpret_cast<const uint4*>(src + cc * 8);
+      }
+    }
+  }
+}
+
+// grid (rows, heads, b): rows [0, seqlen_knew) are new K/V rows (heads < h_k), rows
+// [seqlen_knew, seqlen_knew + seqlen_q) are Q rows to rotate (only when rotary is on).
+template <typename T>
+__global__ void __launch_bounds__(32) fa_append_kernel(const AppendParams a) {
+  const int row = blockIdx.x, head = blockIdx.y, b = blockIdx.z;
+  const int tid = threadIdx.x;
+  const int cache_len = a.cache_seqlens[b];
+  const int half = a.rotary_dim / 2;
+  if (row < a.seqlen_knew) {
+    if (head >= a.h_k) return;
+    const int pos = cache_len + row;
+    int64_t koff, voff;
+    if (a.block_table) {
+      const int pg = min(pos / a.page_block_size, a.max_blocks_per_seq - 1);
+      const int blk = a.block_table[(int64_t)b * a.block_table_batch_stride + pg];
+      const int in_page = pos - (pos / a.page_block_size) * a.page_block_size;
+      koff = (int64_t)blk * a.k_batch_stride + (int64_t)in_page * a.k_row_stride;
+      voff = (int64_t)blk * a.v_batch_stride + (int64_t)in_page * a.v_row_stride;
+    } else {
+      const int kb = a.cache_batch_idx ? a.cache_batch_idx[b] : b;
+      if (pos >= a.seqlen_k) return;   // cache full: the reference would write out of bounds
+      koff = (int64_t)kb * a.k_batch_stride + (int64_t)pos * a.k_row_stride;
+      voff = (int64_t)kb * a.v_batch_stride + (int64_t)pos * a.v_row_stride;
+    }
+    const T* ksrc = reinterpret_cast<const T*>(a.knew) + (int64_t)b * a.knew_batch_stride + (int64_t)row * a.knew_row_stride + (int64_t)head * a.knew_head_stride;
+    const T* vsrc = reinterpret_cast<const T*>(a.vnew) + (int64_t)b * a.vnew_batch_stride + (int64_t)row * a.vnew_row_stride + (int64_t)head * a.vnew_head_stride;
+    T* kdst = reinterpret_cast<T*>(a.kcache) + koff + (int64_t)head * a.k_head_stride;
+    T* vdst = reinterpret_cast<T*>(a.vcache) + voff + (int64_t)head * a.v_head_stride;
+    const int rp = min(pos, max(a.seqlen_ro - 1, 0));
+    rotate_row<T>(ksrc, kdst, a.d, a.rotary_dim, a.is_rotary_interleaved,
+                  reinterpret_cast<const T*>(a.rotary_cos) + (int64_t)rp * half,
+                  reinterpret_cast<const T*>(a.rotary_sin) + (int64_t)rp * half, tid, 32);
+    rotate_row<T>(vsrc, vdst, a.d, 0, true, nullptr, nullptr, tid, 32);
+  } else {
+    const int qpos = row - a.seqlen_knew;
+    if (head >= a.h || a.q_rot == nullptr) return;
+    const int pos = cache_len + (a.rot_by_qpos ? qpos : 0);
+    const int rp = min(pos, max(a.seqlen_ro - 1, 0));
+    const T* qsrc = reinterpret_cast<const T*>(a.q) + (int64_t)b * a.q_batch_stride + (int64_t)qpos * a.q_row_stride + (int64_t)head * a.q_head_stride;
+    T* qdst = reinterpret_cast<T*>(a.q_rot) + (((int64_t)b * a.seqlen_q + qpos) * a.h + head) * a.d;
+    rotate_row<T>(qsrc, qdst, a.d, a.rotary_dim, a.is_rotary_interleaved,
+                  reinterpret_cast<const T*>(a.rotary_cos) + (int64_t)rp * half,
+                  reinterpret_cast<const T*>(a.rotary_sin) + (int64_t)rp * half, tid, 32);
+  }
+}
+
+cudaError_t launch_append(const AppendParams& a, bool is_bf16, cudaStream_t stream) {
+  const int rows = a.seqlen_knew + (a.q_rot ? a.seqlen_q : 0);
+  if (rows == 0) return cudaSuccess;
+  dim3 grid(rows, a.q_rot ? max(a.h, a.h_k) : a.h_k, a.b);
+  if (is_bf16) fa_append_kernel<__nv_bfloat16><<<grid, 32, 0, stream>>>(a);
+  else fa_append_kernel<__half><<<grid, 32, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+
+}  // namespace fa

@@ -26,6 +26,23 @@ struct CombineParams {
 };
 cudaError_t launch_combine(const CombineParams& c, cudaStream_t stream);
 
+// fa_append.cu — append new K/V rows to the cache (+ rotary on K and Q).
+struct AppendParams {
+  const void* knew; const void* vnew; void* kcache; void* vcache;
+  const void* q; void* q_rot;                 // q_rot: (b,seqlen_q,h,d) contiguous, or NULL
+  int64_t knew_batch_stride, knew_row_stride, knew_head_stride;
+  int64_t vnew_batch_stride, vnew_row_stride, vnew_head_stride;
+  int64_t k_batch_stride, k_row_stride, k_head_stride;
+  int64_t v_batch_stride, v_row_stride, v_head_stride;
+  int64_t q_batch_stride, q_row_stride, q_head_stride;
+  int b, h, h_k, d, seqlen_q, seqlen_k, seqlen_knew;
+  const int* cache_seqlens; const int* cache_batch_idx;
+  const int* block_table; int64_t block_table_batch_stride; int page_block_size, max_blocks_per_seq;
+  const void* rotary_cos; const void* rotary_sin; int rotary_dim, seqlen_ro, is_rotary_interleaved;
+  int rot_by_qpos;                            // causal or local: q row i rotated at cache_len + i
+};
+cudaError_t launch_append(const AppendParams& a, bool is_bf16, cudaStream_t stream);
+
 // fa_prefill_tc5.cu — tcgen05/TMA/TMEM prefill kernel, d in {64,128}.
 bool tc5_supported(const KParams& p);
 cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k,

@@ -3,6 +3,7 @@
 // Bit layouts follow the PTX ISA "tcgen05" chapter (matrix descriptor, instruction descriptor
 // for .kind::f16); no CUTLASS/CuTe code is used.
 #pragma once
+#include <cstdio>
 #include "fa_common.cuh"
 
 namespace fa {
@@ -30,8 +31,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   return ok != 0;
 }
+// Bounded wait: a pipeline bug must surface as a trap (launch failure), never as a hung GPU.
+#ifndef FA_MBAR_TIMEOUT_CYCLES
+#define FA_MBAR_TIMEOUT_CYCLES 4000000000ll   /* ~2 s at 1.9 GHz; 0 disables the check */
+#endif
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {}
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (FA_MBAR_TIMEOUT_CYCLES > 0 && clock64() - t0 > FA_MBAR_TIMEOUT_CYCLES) {
+      printf("fa_b200: mbarrier timeout block=(%d,%d,%d) thread=%d bar=0x%x parity=%u\n", blockIdx.x, blockIdx.y,
+             blockIdx.z, threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
 }
 
 // ----------------------------------------------------------------------------- proxies / fences
