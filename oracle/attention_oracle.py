@@ -270,5 +270,11 @@ def attention_ref_varlen(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, wind
         o, _ = attention_ref(qi, ki, vi, attn_bias=bias, causal=causal, window_size=window_size,
                              upcast=upcast, reorder_ops=reorder_ops)
         out[q0:q1] = o[0]
-        lse[i, :, :q1 - q0] = lse_ref(qi, ki, attn_bias=bias, causal=causal, window_size=window_size)[0]
+        l_i = lse_ref(qi, ki, attn_bias=bias, causal=causal, window_size=window_size)[0]
+        if bias is not None and causal:
+            # kernel convention: causal ALiBi bias is slope*j (csrc/flash_attn/src/mask.h:181), the
+            # test helper's is slope*(j-(sk-1)) (tests/test_flash_attn.py:38-39): same out, LSE
+            # differs by the row-constant slope*(sk-1)
+            l_i = l_i + sl.float().view(-1, 1).cpu() * (k1 - k0 - 1)
+        lse[i, :, :q1 - q0] = l_i
     return out, lse

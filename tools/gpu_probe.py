@@ -103,8 +103,13 @@ def run_case(spec):
         ref32, _ = orc.attention_ref(q, k, v, attn_bias=bias, causal=causal, window_size=window)
         out_pt, _ = orc.attention_ref(q, k, v, attn_bias=bias, causal=causal, window_size=window, upcast=False, reorder_ops=True)
         lref = orc.lse_ref(q, k, attn_bias=bias, causal=causal, window_size=window)
-        ork = _util.ref_kernel_fwd(q, k, v, causal, window, slopes)[0] if refk else None
+        if slopes is not None and causal:   # the kernel's causal ALiBi bias is slope*j (src/mask.h:181),
+            lref = lref + slopes.view(b, h, 1) * (sk - 1)   # the oracle's slope*(j-(sk-1)): constant row shift
+        ork, lrk = _util.ref_kernel_fwd(q, k, v, causal, window, slopes) if refk else (None, None)
         res.update(errs(out, ref32, out_pt, ork))
+        if lrk is not None:
+            finr = torch.isfinite(lrk) & torch.isfinite(lse)
+            res["lse_vs_refk"] = (lse[finr] - lrk[finr]).abs().max().item() if finr.any() else 0.0
         fin = torch.isfinite(lref)
         res["lse_err"] = (lse[fin] - lref[fin]).abs().max().item() if fin.any() else 0.0
         res["lse_inf_ok"] = bool((torch.isinf(lse) == torch.isinf(lref)).all().item())
@@ -182,6 +187,8 @@ def run_case(spec):
         out_pt, _ = orc.attention_ref(q, kfull, vfull, None, kpm, bias, causal=causal, window_size=window,
                                       upcast=False, reorder_ops=True)
         lref = orc.lse_ref(q, kfull, kpm, None, bias, causal=causal, window_size=window)
+        if slopes is not None and causal:
+            lref = lref + slopes.view(b, h, 1) * (S - 1)
         ork = None
         if refk and slopes is None:
             ork = _util.ref_kernel_kvcache(q, kc, vc, lens_d, bt, causal, window, spec["splits"])[0]

@@ -72,13 +72,22 @@ __global__ void __launch_bounds__(128) fa_combine_kernel(const CombineParams c) 
   for (int i = 0; i < 4; i++) wgt[i] = empty ? 0.f : expf(ls[i] - lse);
 
   const PT* part = reinterpret_cast<const PT*>(c.o_part);
-  for (int col = lane * 4; col < c.d; col += 128) {
+  for (int col0 = 0; col0 < c.d; col0 += 128) {   // warp-uniform trip count: the shuffles need all lanes
+    const int col = col0 + lane * 4;
+    const bool live = col < c.d;
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int s = 0; s < S; s++) {
-      float w = __shfl_sync(0xffffffffu, wgt[s >> 5], s & 31);
-      float4 x = load4<PT>(part + ((int64_t)s * rows + row) * c.d + col);
-      acc.x += w * x.x; acc.y += w * x.y; acc.z += w * x.z; acc.w += w * x.w;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      for (int sl = 0; sl < 32 && i * 32 + sl < S; sl++) {
+        const int s = i * 32 + sl;
+        float w = __shfl_sync(0xffffffffu, wgt[i], sl);
+        if (live) {
+          float4 x = load4<PT>(part + ((int64_t)s * rows + row) * c.d + col);
+          acc.x += w * x.x; acc.y += w * x.y; acc.z += w * x.z; acc.w += w * x.w;
+        }
+      }
     }
+    if (!live) continue;
     if constexpr (OUT_DT == 0) {
       *reinterpret_cast<float4*>(reinterpret_cast<float*>(c.o) + obase + col) = acc;
     } else if constexpr (OUT_DT == 1) {

@@ -173,7 +173,8 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
               [&](int row, int col, float x) -> float {
                 const int i2 = row >> 4, r2 = (row >> 3) & 1;
                 const int j = col0 + col;
-                if (has_alibi) x -= row_slope[i2][r2] * fabsf((float)(row_shift[i2][r2] - j));
+                if (has_alibi) x += p.is_causal ? row_slope[i2][r2] * (float)j     // src/mask.h:181
+                                                : -row_slope[i2][r2] * fabsf((float)(row_shift[i2][r2] - j));
                 return (j >= row_lo[i2][r2] && j < row_hi[i2][r2]) ? x : -INFINITY;
               });
     __syncwarp();

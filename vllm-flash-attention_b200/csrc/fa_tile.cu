@@ -122,7 +122,8 @@ __global__ void __launch_bounds__(128) fa_tile_kernel(const __grid_constant__ KP
               [&](int row, int col, float x) -> float {
                 const int r2 = (row >> 3) & 1;
                 const int j = col0 + col;
-                if (has_alibi) x -= slope2 * fabsf((float)(row_shift[r2] - j));
+                if (has_alibi) x += p.is_causal ? slope2 * (float)j                // src/mask.h:181
+                                                : -slope2 * fabsf((float)(row_shift[r2] - j));
                 return (j >= row_lo[r2] && j < row_hi[r2]) ? x : -INFINITY;
               });
     __syncthreads();
