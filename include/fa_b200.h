@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 1
+#define FA_B200_ABI_VERSION 2
 
 enum {
   FA_OK = 0,
@@ -99,6 +99,12 @@ typedef struct FaFwdParams {
   int32_t num_splits;    /* in: 0 = heuristic, >=1 forced; out: splits used */
   void* workspace;       /* >= fa_b200_workspace_bytes(p) bytes, or NULL when that is 0 */
   size_t workspace_bytes;
+  /* fwd_kvcache only.  1 = partial-result mode for a KV range that is one shard of a longer
+   * sequence (sequence-sharded decode): `o` is FP32 laid out (b,h,seqlen_q,d) contiguous
+   * (strides must say so), softmax_lse is (b,h,seqlen_q) with -inf (not +inf) for rows that see no
+   * key in this shard — exactly the per-split partials of the reference's split-KV kernel
+   * (flash_api.cpp:212-213, flash_fwd_kernel.h:513-552), ready for fa_b200_combine. */
+  int32_t partial_out;
 
   /* ---- tuning / diagnostics ---- */
   int32_t num_sms;       /* 0 = query the device */
@@ -135,14 +141,17 @@ int fa_b200_fwd_kvcache(FaFwdParams* p, void* stream);
  * then runs fa_b200_fwd_kvcache with knew/vnew/rotary cleared, seqlen_knew kept, q = rotated q. */
 int fa_b200_append_kv(FaFwdParams* p, void* stream);
 
-/* Merge `n` partial results (o_part: (n,rows,d) fp32 or bf16/fp16, lse_part: (n,rows) fp32)
- * into o (rows,d) + lse (rows): lse = logsumexp_s lse_s, o = sum_s exp(lse_s-lse) o_s.
- * Same algebra as combine_attn_seqk_parallel (flash_fwd_kernel.h:1092-1250); used for the
- * in-GPU split-KV merge and for the cross-GPU (out,lse) merge after an allgather.
- * part_dtype / out_dtype: 0 = fp32, 1 = bf16, 2 = fp16. */
+/* Merge `n` partial results into o (rows,d) + lse (rows): lse = logsumexp_s lse_s,
+ * o = sum_s exp(lse_s-lse) o_s — the algebra of combine_attn_seqk_parallel
+ * (flash_fwd_kernel.h:1092-1250); used for the in-GPU split-KV merge and for the cross-GPU
+ * (out,lse) merge after an allgather.  Partial s lives at o_part + s*part_stride (rows x d
+ * elements, row-major) and lse_part + s*lse_stride (rows floats); strides are in ELEMENTS, so a
+ * packed per-rank record [o (rows*d) | lse (rows)] of fp32 can be merged in place with
+ * part_stride = lse_stride = rows*(d+1).  part_dtype / out_dtype: 0 = fp32, 1 = bf16, 2 = fp16.
+ * Rows whose partials are all empty (-inf) get o = 0 and lse = +inf (flash_fwd_kernel.h:1156,1164). */
 int fa_b200_combine(const void* o_part, const float* lse_part, void* o, float* lse,
-                    int32_t n, int64_t rows, int32_t d, int32_t part_dtype, int32_t out_dtype,
-                    void* stream);
+                    int32_t n, int64_t rows, int32_t d, int64_t part_stride, int64_t lse_stride,
+                    int32_t part_dtype, int32_t out_dtype, void* stream);
 
 #ifdef __cplusplus
 }

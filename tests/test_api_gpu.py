@@ -114,7 +114,7 @@ def test_combine_entry_point():
     l_p[2] = float("-inf")
     l_p[:, 5] = float("-inf")
     o = torch.empty(rows, d, device="cuda", dtype=torch.bfloat16); lse = torch.empty(rows, device="cuda")
-    check(lib.fa_b200_combine(o_p.data_ptr(), l_p.data_ptr(), o.data_ptr(), lse.data_ptr(), n, rows, d, 0, 1,
+    check(lib.fa_b200_combine(o_p.data_ptr(), l_p.data_ptr(), o.data_ptr(), lse.data_ptr(), n, rows, d, rows * d, rows, 0, 1,
                               torch.cuda.current_stream().cuda_stream))
     oc, lc = orc.combine_ref(o_p.cpu(), l_p.cpu())
     assert (o.float().cpu() - oc).abs().max() < 2e-2
@@ -233,5 +233,10 @@ def test_full_size_configs_vs_reference_kernel(cfg):
     assert not torch.isnan(out.float()).any()
     assert (out.float() - rk.float()).abs().max() < 2e-2
     n = min(lse.shape[-1], rl.shape[-1])
-    fin = torch.isfinite(rl[..., :n]) & (rl[..., :n] != 0)
+    fin = torch.isfinite(rl[..., :n])
+    if cfg == "C2_varlen_prefill":
+        # varlen lse is (b,h,max_seqlen_q), padded: positions past each sequence's length are
+        # never written by either kernel (flash_api.cpp:578 allocates with torch::empty)
+        valid = torch.arange(n, device=dev).view(1, 1, -1) < torch.tensor(lens, device=dev).view(-1, 1, 1)
+        fin = fin & valid
     assert (lse[..., :n][fin] - rl[..., :n][fin]).abs().max() < 2e-3

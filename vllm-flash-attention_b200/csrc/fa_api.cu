@@ -112,6 +112,16 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   k.cache_batch_idx = a->cache_batch_idx;
   k.seqlen_knew = a->seqlen_knew;   // rows already appended by fa_b200_append_kv
   k.lse_seq_stride = a->seqlen_q;
+  k.partial = 0;
+  if (a->partial_out) {
+    FA_CHECK(op == OP_KVCACHE, "partial_out is only valid for fwd_kvcache");
+    FA_CHECK(a->softmax_lse != nullptr, "partial_out needs softmax_lse");
+    FA_CHECK(a->o_row_stride == a->d && a->o_head_stride == (int64_t)a->seqlen_q * a->d &&
+             a->o_batch_stride == (int64_t)a->h * a->seqlen_q * a->d,
+             "partial_out: o must be fp32 (b,h,seqlen_q,d) contiguous");
+    FA_CHECK((reinterpret_cast<uintptr_t>(a->o) & 15) == 0, "partial_out: o must be 16-byte aligned");
+    k.partial = 1;
+  }
 
   // ---- mask normalisation (flash_api.cpp:289-294 and set_params_fprop :119-126) ----
   int wl = a->window_left, wr = a->window_right;
@@ -135,11 +145,11 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   k.num_splits = 1;
   if (kernel == FA_KERNEL_NONE) {
     if (decode_supported(a->d, rows)) kernel = FA_KERNEL_DECODE;
-    else if (tc5_supported(k)) kernel = FA_KERNEL_TC5_PREFILL;
+    else if (!k.partial && tc5_supported(k)) kernel = FA_KERNEL_TC5_PREFILL;
     else kernel = FA_KERNEL_TILE;
   }
   if (kernel == FA_KERNEL_DECODE) FA_CHECK(decode_supported(a->d, rows), "decode kernel: d/rows not supported");
-  if (kernel == FA_KERNEL_TC5_PREFILL) FA_CHECK(tc5_supported(k), "tcgen05 prefill kernel: shape/layout not supported");
+  if (kernel == FA_KERNEL_TC5_PREFILL) FA_CHECK(!k.partial && tc5_supported(k), "tcgen05 prefill kernel: shape/layout not supported");
   if (kernel == FA_KERNEL_TILE) FA_CHECK(tile_supported(a->d), "head dimension must be a multiple of 32 (reference build: -DFLASHATTENTION_DISABLE_UNEVEN_K)");
   pl->kernel = kernel;
 
@@ -185,6 +195,10 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
     if ((reinterpret_cast<uintptr_t>(k.o_accum) & 15) != 0)   // keep float4 alignment
       k.o_accum = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(k.o_accum) + 15) & ~(uintptr_t)15);
   }
+  if (k.partial && pl.num_splits == 1) {   // the single "split" IS the result: (b,h,sq,d) fp32 + lse
+    k.o_accum = reinterpret_cast<float*>(a->o);
+    k.lse_accum = a->softmax_lse;
+  }
   cudaError_t e = cudaSuccess;
   switch (pl.kernel) {
     case FA_KERNEL_DECODE: e = launch_decode(k, pl.is_bf16, stream); break;
@@ -199,7 +213,10 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
     c.o_part = k.o_accum; c.lse_part = k.lse_accum; c.o = a->o; c.lse = a->softmax_lse;
     c.n_splits = pl.num_splits; c.b = a->b; c.h = a->h; c.sq = a->seqlen_q; c.d = a->d;
     c.o_batch_stride = a->o_batch_stride; c.o_row_stride = a->o_row_stride; c.o_head_stride = a->o_head_stride;
-    c.cu_seqlens_q = a->cu_seqlens_q; c.part_dtype = 0; c.out_dtype = pl.is_bf16 ? 1 : 2;
+    c.cu_seqlens_q = a->cu_seqlens_q; c.part_dtype = 0; c.out_dtype = k.partial ? 0 : (pl.is_bf16 ? 1 : 2);
+    c.part_split_stride = (int64_t)a->b * a->h * a->seqlen_q * a->d;
+    c.lse_split_stride = (int64_t)a->b * a->h * a->seqlen_q;
+    c.empty_neg_inf = k.partial;
     e = launch_combine(c, stream);
     if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in combine kernel launch: %s", cudaGetErrorString(e));
     a->launches = 2;
@@ -233,17 +250,23 @@ extern "C" int fa_b200_fwd_kvcache(FaFwdParams* p, void* stream) {
 }
 
 extern "C" int fa_b200_combine(const void* o_part, const float* lse_part, void* o, float* lse, int32_t n,
-                               int64_t rows, int32_t d, int32_t part_dtype, int32_t out_dtype, void* stream) {
+                               int64_t rows, int32_t d, int64_t part_stride, int64_t lse_stride,
+                               int32_t part_dtype, int32_t out_dtype, void* stream) {
   g_err[0] = 0;
   if (!o_part || !lse_part || !o) return fail(FA_ERR_INVALID, "combine: NULL pointer");
   if (n < 1 || n > 128) return fail(FA_ERR_INVALID, "combine: n must be in [1,128]");
   if (d % 4 != 0 || d <= 0) return fail(FA_ERR_INVALID, "combine: d must be a positive multiple of 4");
-  if (rows > 0x7fffffff) return fail(FA_ERR_INVALID, "combine: too many rows");
+  if (rows > 0x7fffffff || rows < 0) return fail(FA_ERR_INVALID, "combine: bad row count");
+  if (part_stride < rows * d || lse_stride < rows) return fail(FA_ERR_INVALID, "combine: partial strides smaller than one partial");
+  const int esz = part_dtype == 0 ? 4 : 2;
+  if ((reinterpret_cast<uintptr_t>(o_part) % (4 * esz)) != 0 || (part_stride * esz) % (4 * esz) != 0)
+    return fail(FA_ERR_INVALID, "combine: partials must be aligned to 4 elements");
   CombineParams c;
   c.o_part = o_part; c.lse_part = lse_part; c.o = o; c.lse = lse;
   c.n_splits = n; c.b = 1; c.h = 1; c.sq = (int)rows; c.d = d;
   c.o_batch_stride = 0; c.o_row_stride = d; c.o_head_stride = 0; c.cu_seqlens_q = nullptr;
   c.part_dtype = part_dtype; c.out_dtype = out_dtype;
+  c.part_split_stride = part_stride; c.lse_split_stride = lse_stride; c.empty_neg_inf = 0;
   cudaError_t e = launch_combine(c, (cudaStream_t)stream);
   if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in combine kernel launch: %s", cudaGetErrorString(e));
   return FA_OK;

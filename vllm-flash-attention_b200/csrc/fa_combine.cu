@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(128) fa_combine_kernel(const CombineParams c) 
 #pragma unroll
   for (int i = 0; i < 4; i++) {
     int s = lane + 32 * i;
-    ls[i] = s < S ? c.lse_part[(int64_t)s * rows + row] : -INFINITY;
+    ls[i] = s < S ? c.lse_part[(int64_t)s * c.lse_split_stride + row] : -INFINITY;
     mx = fmaxf(mx, ls[i]);
   }
 #pragma unroll
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(128) fa_combine_kernel(const CombineParams c) 
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
   const bool empty = !(sum > 0.f);
-  const float lse = empty ? INFINITY : logf(sum) + mx_safe;
+  const float lse = empty ? (c.empty_neg_inf ? -INFINITY : INFINITY) : logf(sum) + mx_safe;
   if (lane == 0 && c.lse) c.lse[row] = lse;
   float wgt[4];
 #pragma unroll
@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(128) fa_combine_kernel(const CombineParams c) 
         const int s = i * 32 + sl;
         float w = __shfl_sync(0xffffffffu, wgt[i], sl);
         if (live) {
-          float4 x = load4<PT>(part + ((int64_t)s * rows + row) * c.d + col);
+          float4 x = load4<PT>(part + (int64_t)s * c.part_split_stride + row * c.d + col);
           acc.x += w * x.x; acc.y += w * x.y; acc.z += w * x.z; acc.w += w * x.w;
         }
       }

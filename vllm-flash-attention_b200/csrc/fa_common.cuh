@@ -34,6 +34,7 @@ struct KParams {
   int seqlen_knew;                              // keys appended this call (already in cache)
   int num_splits;
   int lse_seq_stride;                           // seqlen_q used for lse/accum row indexing
+  int partial;                                  // write fp32 partials (o_accum/lse_accum, -inf for empty rows) even with 1 split
 };
 
 // Per-sequence geometry — the analogue of BlockInfo (reference src/block_info.h:11-42).

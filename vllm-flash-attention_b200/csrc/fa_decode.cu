@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
         const bool empty = !(lt > 0.f);
         row_inv[row] = empty ? 0.f : 1.f / lt;
         // natural-log LSE = max*scale + ln(sum) (softmax.h:179); m is in log2 units
-        row_lse[row] = empty ? (p.num_splits > 1 ? -INFINITY : INFINITY)
+        row_lse[row] = empty ? ((p.num_splits > 1 || p.partial) ? -INFINITY : INFINITY)
                              : mt * 0.6931471805599453f + __logf(lt);
       }
     }
@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
 
   // ---- write out ----
   const int Rw = min(R, ROWS);
-  if (p.num_splits > 1) {
+  if ((p.num_splits > 1 || p.partial)) {
     // fp32 partials, (split, b, h, sq[, d]) like the reference's accum buffers (flash_api.cpp:212-213)
     for (int idx = threadIdx.x; idx < Rw * (D / 4); idx += NW * 32) {
       int r = idx / (D / 4), c4 = idx % (D / 4);

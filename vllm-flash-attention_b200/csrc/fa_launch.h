@@ -23,6 +23,8 @@ struct CombineParams {
   int64_t o_batch_stride, o_row_stride, o_head_stride;
   const int* cu_seqlens_q;
   int part_dtype, out_dtype;
+  int64_t part_split_stride, lse_split_stride;   // elements between consecutive partials
+  int empty_neg_inf;                             // all-empty rows report lse = -inf (partial-result mode)
 };
 cudaError_t launch_combine(const CombineParams& c, cudaStream_t stream);
 

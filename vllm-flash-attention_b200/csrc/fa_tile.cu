@@ -138,11 +138,11 @@ __global__ void __launch_bounds__(128) fa_tile_kernel(const __grid_constant__ KP
   for (int r = 0; r < 2; r++) {
     const bool empty = !(attn.l[0][r] > 0.f);
     inv[r] = empty ? 0.f : 1.f / attn.l[0][r];
-    lse[r] = empty ? (p.num_splits > 1 ? -INFINITY : INFINITY)
+    lse[r] = empty ? ((p.num_splits > 1 || p.partial) ? -INFINITY : INFINITY)
                    : attn.m[0][r] * 0.6931471805599453f + __logf(attn.l[0][r]);
   }
   const int row_base = m0 + warp * 16;
-  if (p.num_splits > 1) {
+  if ((p.num_splits > 1 || p.partial)) {
 #pragma unroll
     for (int r = 0; r < 2; r++) {
       int qpos = row_base + (lane >> 2) + r * 8;

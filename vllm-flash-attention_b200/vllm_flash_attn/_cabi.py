@@ -13,6 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FA_B200_LIB", os.path.join(_HERE, "libfa_b200.so"))
 
 FA_OK = 0
+ABI_VERSION = 2
 FA_KERNEL_NONE, FA_KERNEL_TC5_PREFILL, FA_KERNEL_TILE, FA_KERNEL_DECODE = 0, 1, 2, 3
 OP_FWD, OP_VARLEN, OP_KVCACHE = 0, 1, 2
 
@@ -42,7 +43,7 @@ class FaFwdParams(C.Structure):
         ("seqlen_knew", _i32),
         ("rotary_cos", _vp), ("rotary_sin", _vp),
         ("rotary_dim", _i32), ("seqlen_ro", _i32), ("is_rotary_interleaved", _i32),
-        ("num_splits", _i32), ("workspace", _vp), ("workspace_bytes", C.c_size_t),
+        ("num_splits", _i32), ("workspace", _vp), ("workspace_bytes", C.c_size_t), ("partial_out", _i32),
         ("num_sms", _i32), ("force_kernel", _i32), ("kernel_used", _i32), ("launches", _i32),
     ]
 
@@ -73,8 +74,8 @@ def _load():
         fn.restype = C.c_int
         fn.argtypes = [C.POINTER(FaFwdParams), _vp]
     lib.fa_b200_combine.restype = C.c_int
-    lib.fa_b200_combine.argtypes = [_vp, _vp, _vp, _vp, _i32, _i64, _i32, _i32, _i32, _vp]
-    if lib.fa_b200_abi_version() != 1:
+    lib.fa_b200_combine.argtypes = [_vp, _vp, _vp, _vp, _i32, _i64, _i32, _i64, _i64, _i32, _i32, _vp]
+    if lib.fa_b200_abi_version() != ABI_VERSION:
         raise ImportError("libfa_b200.so ABI version mismatch")
     if lib.fa_b200_params_size() != C.sizeof(FaFwdParams):
         raise ImportError(

@@ -219,10 +219,15 @@ def varlen_fwd(q, k, v, out_, cu_seqlens_q, cu_seqlens_k, seqused_k, block_table
 
 def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_, cache_batch_idx_,
                 block_table_, alibi_slopes_, out_, softmax_scale, is_causal, window_size_left,
-                window_size_right, is_rotary_interleaved, num_splits) -> List[torch.Tensor]:
+                window_size_right, is_rotary_interleaved, num_splits, *, _partial_buf=None) -> List[torch.Tensor]:
     """mha_fwd_kvcache (flash_api.cpp:671-937).  q (b,sq,h,d); cache (b_c,sk,hk,d) or paged
     (num_blocks,page,hk,d) with block_table (b,max_blocks); optional new k/v (b,sk_new,hk,d) appended
-    in place at cache_seqlens (with rotary on k and q).  Returns [out, softmax_lse]."""
+    in place at cache_seqlens (with rotary on k and q).  Returns [out, softmax_lse].
+
+    ``_partial_buf`` (extension used by vllm_flash_attn.sharded): a 1-D fp32 tensor of
+    b*h*sq*(d+1) elements; the call then runs in the C ABI's partial_out mode and writes the packed
+    record [o (b,h,sq,d) | lse (b,h,sq)] into it (lse = -inf for rows with no key in this shard),
+    returning views of the two parts."""
     _check_qkv(q, kcache, vcache)
     dev = q.device
     _chk(q.dim() == 4 and kcache.dim() == 4 and vcache.dim() == 4, "q, kcache, vcache must be 4-D")
@@ -248,7 +253,16 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
     _chk(tuple(vcache.shape) == tuple(kcache.shape) and kcache.shape[3] == d_og, "kcache/vcache shape mismatch")
     _chk(d_og % 8 == 0, "fwd_kvcache: head dimension must be a multiple of 8 (cache cannot be padded in place)")
     d = d_og
-    if out_ is not None:
+    partial = _partial_buf is not None
+    if partial:
+        rows = b * h * sq
+        _chk(out_ is None, "out= cannot be combined with partial mode")
+        _chk(_partial_buf.dtype == torch.float32 and _partial_buf.is_cuda and _partial_buf.device == dev and
+             _partial_buf.is_contiguous() and _partial_buf.numel() == rows * (d + 1),
+             "partial buffer must be a contiguous fp32 CUDA tensor of b*h*sq*(d+1) elements")
+        out = _partial_buf[: rows * d].view(b, h, sq, d)
+        lse = _partial_buf[rows * d:].view(b, h, sq)
+    elif out_ is not None:
         _chk(out_.dtype == q.dtype, "Output must have the same dtype as inputs")
         _chk(out_.is_cuda and out_.device == dev, "Output must be on the same device")
         _chk(out_.stride(-1) == 1, "Output tensor must have contiguous last dimension")
@@ -258,7 +272,8 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
         out = out_
     else:
         out = torch.empty_like(q)
-    lse = torch.empty((b, h, sq), dtype=torch.float32, device=dev)
+    if not partial:
+        lse = torch.empty((b, h, sq), dtype=torch.float32, device=dev)
     if seqlens_k_ is not None:
         _i32_dev(seqlens_k_, "seqlens_k", dev)
         _chk(seqlens_k_.is_contiguous() and tuple(seqlens_k_.shape) == (b,), "seqlens_k must have shape (batch_size)")
@@ -272,7 +287,11 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
         P.q_batch_stride, P.q_row_stride, P.q_head_stride = q.stride(0), q.stride(1), q.stride(2)
         P.k_batch_stride, P.k_row_stride, P.k_head_stride = kcache.stride(0), kcache.stride(1), kcache.stride(2)
         P.v_batch_stride, P.v_row_stride, P.v_head_stride = vcache.stride(0), vcache.stride(1), vcache.stride(2)
-        P.o_batch_stride, P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
+        if partial:   # (b,h,sq,d) fp32
+            P.o_batch_stride, P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(2), out.stride(1)
+            P.partial_out = 1
+        else:
+            P.o_batch_stride, P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
         P.b, P.seqlen_q, P.seqlen_k, P.h, P.h_k, P.d = b, sq, sk, h, hk, d
         P.is_bf16 = int(q.dtype == torch.bfloat16)
         P.softmax_scale = softmax_scale
