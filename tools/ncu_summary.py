@@ -1,0 +1,19 @@
+"""Summarise an .ncu-rep (raw page) into the handful of metrics the roofline discussion needs.
+  python tools/ncu_summary.py gpurun_out/prof.ncu-rep [extra_regex]"""
+import csv, io, re, subprocess, sys
+rep = sys.argv[1]
+extra = sys.argv[2] if len(sys.argv) > 2 else None
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(raw)))
+hdr, units = rows[0], rows[1]
+pat = re.compile(r"(gpu__time_duration\.sum|dram__bytes_(read|write)\.sum$|dram__throughput\.avg\.pct|"
+                 r"sm__pipe_tensor.*cycles_active.*pct|sm__inst_executed_pipe_(xu|tensor|fma|alu|lsu|uniform|tmem).*pct|sm__warps_active\.avg\.pct|"
+                 r"launch__registers_per_thread|launch__grid_size|launch__block_size|launch__occupancy_limit|"
+                 r"sm__throughput\.avg\.pct|smsp__issue_active\.avg\.pct|l1tex__throughput\.avg\.pct|lts__throughput\.avg\.pct|"
+                 r"smsp__average_warps?_issue_stalled.*_per_issue_active|smsp__cycles_active\.avg|sm__cycles_elapsed\.max|"
+                 r"smsp__inst_executed\.sum$|local_(load|store))" + (("|" + extra) if extra else ""))
+for r in rows[2:]:
+    print("== kernel:", r[hdr.index("Kernel Name")][:90], "grid", r[hdr.index("Grid Size")], "block", r[hdr.index("Block Size")])
+    for h, u, v in zip(hdr, units, r):
+        if pat.search(h):
+            print(f"  {h} [{u}] = {v}")

@@ -10,7 +10,7 @@
 // 2^8), which changes the reference max `m` used inside exp2 but not the normalised result.
 //
 // CTA = 256 query rows of one (sequence, head) as two 128-row tiles that ping-pong through the
-// tensor core, 10 warps:
+// tensor core, 12 warps (warps 10-11 idle: setmaxnreg moves registers by whole warpgroups):
 //   warps 0-3  softmax warpgroup of Q tile 0   (TMEM lanes 0..127 = rows; thread = row)
 //   warps 4-7  softmax warpgroup of Q tile 1
 //   warp  8    TMA producer (Q tiles once, then K_j, V_j through an NS-slot ring)
@@ -28,7 +28,8 @@ using namespace sm100;
 
 constexpr int TC5_BM = 128;        // rows per Q tile (UMMA M)
 constexpr int TC5_BN = 128;        // keys per KV tile (UMMA N for QK^T)
-constexpr int TC5_THREADS = 320;
+constexpr int TC5_THREADS = 384;       // 3 warpgroups; warps 10-11 only donate registers
+constexpr int TC5_REGS_SOFTMAX = 224, TC5_REGS_OTHER = 56;   // 256*224 + 128*56 = 384*168
 constexpr int TC5_PRODUCER_WARP = 8, TC5_MMA_WARP = 9;
 
 struct Tc5Maps { CUtensorMap q, k, v; };
@@ -115,7 +116,10 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_ptr;
 
+  // register re-split by whole warpgroups (setmaxnreg sits at the top of each role so that ptxas
+  // allocates each role against its own budget): the softmax threads hold a full 128-column S row
   if (warp == TC5_PRODUCER_WARP) {
+    setmaxnreg_dec<TC5_REGS_OTHER>();
     // =============================== TMA producer ===============================
     if (elect_one()) {
       for (int t = 0; t < 2; t++) {
@@ -139,6 +143,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
     }
     __syncwarp();
   } else if (warp == TC5_MMA_WARP) {
+    setmaxnreg_dec<TC5_REGS_OTHER>();
     // =============================== MMA issuer ===============================
     constexpr uint32_t idesc_qk = make_idesc(IS_BF16, TC5_BM, TC5_BN, false);
     constexpr uint32_t idesc_pv = make_idesc(IS_BF16, TC5_BM, D, true);
@@ -198,9 +203,12 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
       }
     }
     __syncwarp();
-  } else {
+  } else if (warp < 8) {
+    setmaxnreg_inc<TC5_REGS_SOFTMAX>();
     // =============================== softmax warpgroups ===============================
 #include "fa_prefill_tc5_softmax.inc"
+  } else {
+    setmaxnreg_dec<TC5_REGS_OTHER>();
   }
 
   tc_fence_before();

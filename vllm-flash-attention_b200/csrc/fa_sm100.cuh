@@ -32,20 +32,21 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   return ok != 0;
 }
 // Bounded wait: a pipeline bug must surface as a trap (launch failure), never as a hung GPU.
-#ifndef FA_MBAR_TIMEOUT_CYCLES
-#define FA_MBAR_TIMEOUT_CYCLES 4000000000ll   /* ~2 s at 1.9 GHz; 0 disables the check */
+// try_wait suspends the thread in hardware for a bounded time per call, so the spin count is a
+// coarse clock; the failure path is out of line to keep the hot loop at 3 instructions.
+#ifndef FA_MBAR_SPIN_LIMIT
+#define FA_MBAR_SPIN_LIMIT (1u << 26)   /* 0 disables the check */
 #endif
+// No printf / function call here: a call in the kernel makes ptxas allocate every setmaxnreg region
+// against the smallest budget.  The trap surfaces as cudaErrorLaunchFailure at the next sync.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
+  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (FA_MBAR_TIMEOUT_CYCLES > 0 && clock64() - t0 > FA_MBAR_TIMEOUT_CYCLES) {
-      printf("fa_b200: mbarrier timeout block=(%d,%d,%d) thread=%d bar=0x%x parity=%u\n", blockIdx.x, blockIdx.y,
-             blockIdx.z, threadIdx.x, bar, parity);
-      __trap();
-    }
+    if (FA_MBAR_SPIN_LIMIT != 0u && ++spins > FA_MBAR_SPIN_LIMIT) __trap();
   }
 }
+template <int N> __device__ __forceinline__ void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N)); }
+template <int N> __device__ __forceinline__ void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(N)); }
 
 // ----------------------------------------------------------------------------- proxies / fences
 __device__ __forceinline__ void fence_proxy_async_smem() {   // generic-proxy smem writes -> async proxy (UMMA/TMA)
