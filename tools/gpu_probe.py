@@ -29,7 +29,7 @@ def C(name, kern, kind="dense", **kw):
 
 
 CASES = []
-for pm in ("t", "s"):
+for pm in ("t",):
     sfx = "_P" + pm
     CASES += [
         C("tc5_d128_1tile" + sfx, K_TC5, b=1, h=1, hk=1, sq=128, sk=128, pmode=pm),

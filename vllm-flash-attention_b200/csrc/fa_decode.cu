@@ -281,8 +281,7 @@ template <typename T, int D, int MT, int NW, int STAGES>
 static cudaError_t launch_decode_t(const KParams& p, cudaStream_t stream) {
   using Cfg = DecodeCfg<T, D, MT, NW, STAGES>;
   auto kern = fa_decode_kernel<T, D, MT, NW, STAGES>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-  if (e != cudaSuccess) return e;
+  FA_SET_SMEM_ONCE(kern, Cfg::SMEM);
   dim3 grid(p.num_splits, p.h_k, p.b);
   kern<<<grid, NW * 32, Cfg::SMEM, stream>>>(p);
   return cudaGetLastError();

@@ -5,6 +5,21 @@
 
 namespace fa {
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel instantiation, device): the
+// call costs microseconds, which matters for launch-latency-bound shapes.  Expands inside a
+// function template so the flag array is per instantiation.
+#define FA_SET_SMEM_ONCE(kern, bytes)                                                         \
+  do {                                                                                        \
+    static bool fa_attr_done[64] = {false};                                                   \
+    int fa_dev = 0;                                                                           \
+    cudaGetDevice(&fa_dev);                                                                   \
+    if (fa_dev < 0 || fa_dev >= 64 || !fa_attr_done[fa_dev]) {                                \
+      cudaError_t fa_e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes); \
+      if (fa_e != cudaSuccess) return fa_e;                                                   \
+      if (fa_dev >= 0 && fa_dev < 64) fa_attr_done[fa_dev] = true;                            \
+    }                                                                                         \
+  } while (0)
+
 // fa_decode.cu — rows = seqlen_q*group packed rows must satisfy decode_supported(d, rows).
 bool decode_supported(int d, int rows);
 cudaError_t launch_decode(const KParams& p, bool is_bf16, cudaStream_t stream);

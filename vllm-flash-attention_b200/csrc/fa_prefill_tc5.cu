@@ -1,6 +1,6 @@
 // fa_prefill_tc5.cu — compute-bound prefill / varlen kernel for sm_100a:
 // TMA -> shared memory -> tcgen05.mma with S and O accumulators in TMEM -> online softmax in
-// registers (one thread per query row, no shuffles) -> P back through TMEM (or smem) -> PV MMA.
+// registers (one thread per query row, no shuffles) -> P back through TMEM -> PV MMA.
 //
 // Replaces compute_attn_1rowblock (reference src/flash_fwd_kernel.h:27-470; mma.sync m16n8k16 +
 // cp.async, one 128-row tile per 4-warp CTA, single-buffered K/V).  The arithmetic contract is
@@ -21,10 +21,20 @@
 // S0(j+1) the tensor core runs PV1(j) and QK1(j+1).
 #include "fa_common.cuh"
 #include "fa_sm100.cuh"
+#include <type_traits>
+#include <vector>
 #include "fa_launch.h"
 
 namespace fa {
 using namespace sm100;
+
+// Debug timeline (tools/tc5_trace.py): -DFA_TC5_TRACE builds record clock64 stamps of CTA (0,0,0):
+// trace[role][iteration][event], role 0/1 = softmax warpgroup 0/1 (its first thread), 2 = MMA issuer.
+#ifdef FA_TC5_TRACE
+#define TC5_TRACE(role, iter, ev) do { if (p.trace && trace_cta && (iter) < 128) p.trace[((role) * 128 + (iter)) * 16 + (ev)] = clock64(); } while (0)
+#else
+#define TC5_TRACE(role, iter, ev) do { } while (0)
+#endif
 
 constexpr int TC5_BM = 128;        // rows per Q tile (UMMA M)
 constexpr int TC5_BN = 128;        // keys per KV tile (UMMA N for QK^T)
@@ -36,20 +46,55 @@ struct Tc5Maps { CUtensorMap q, k, v; };
 template <typename T> struct IsBf16 { static constexpr bool value = false; };
 template <> struct IsBf16<__nv_bfloat16> { static constexpr bool value = true; };
 
-template <int D, bool P_TMEM> struct Tc5Cfg {
+template <int D> struct Tc5Cfg {
   static constexpr int ND = D / 64;                         // 64-element (128 B) sub-tiles per row
   static constexpr int SUB_BYTES = 128 * 128;               // 128 rows x 128 B
   static constexpr int TILE_BYTES = ND * SUB_BYTES;         // a Q / K / V tile
-  static constexpr int P_BYTES = P_TMEM ? 0 : 2 * SUB_BYTES;  // 128 x 128 bf16 per Q tile
-  static constexpr int NS = P_TMEM ? (D == 128 ? 5 : 8) : (D == 128 ? 3 : 6);
+  static constexpr int NS = D == 128 ? 5 : 8;
   static constexpr int OFF_Q = 0;
   static constexpr int OFF_KV = 2 * TILE_BYTES;
-  static constexpr int OFF_P = OFF_KV + NS * TILE_BYTES;
-  static constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
+  static constexpr int OFF_BAR = OFF_KV + NS * TILE_BYTES;
   static constexpr int NUM_BARS = 2 /*q*/ + 2 * NS + 2 /*s*/ + 2 /*p*/ + 2 /*o*/;
   static constexpr int SMEM = OFF_BAR + NUM_BARS * 8 + 16 + 1024;   // +1024: manual alignment
   static constexpr int TM_S = 0, TM_O = 256;                // TMEM column bases; tile t adds t*128
 };
+
+// exp2 of 32 scaled scores -> 16 packed bf16/fp16 pairs + row-sum accumulation.
+// The MUFU unit (16 ex2/clk/SM) needs exactly as many cycles per tile as the tensor pipe, so NEMU
+// of every 16 pairs are evaluated on the FMA pipe instead (FA4-style): 2^x = 2^n * 2^r with
+// n = round(x) taken from the magic-number add, r = x - n in [-0.5, 0.5], 2^r by a degree-3
+// minimax polynomial (max rel. error 7.6e-5, 26x below the bf16 rounding of P that follows), and
+// 2^n applied by adding n to the exponent field.  Everything but the exponent add is packed
+// fp32x2.  Inputs are clamped at -126 (result 2^-126 instead of 0), so callers use NEMU = 0 on
+// tiles that contain masked (-inf) scores.
+#ifndef FA_TC5_EMU
+#define FA_TC5_EMU 0
+#endif
+template <typename T, int NEMU>
+__device__ __forceinline__ void tc5_exp_chunk(const uint32_t (&s)[32], const float2 mul2, const float2 nms2,
+                                              float2& la, float2& lb, uint32_t (&pk)[16]) {
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    // packed fp32x2: one FFMA2 scales and shifts two scores, one FADD2 accumulates two sums
+    float2 x = __ffma2_rn(make_float2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), mul2, nms2);
+    float2 pp;
+    if ((i & 1) && (i >> 1) < NEMU) {
+      x.x = fmaxf(x.x, -126.f); x.y = fmaxf(x.y, -126.f);
+      const float2 tt = __fadd2_rn(x, make_float2(12582912.f, 12582912.f));       // 1.5*2^23: low bits = round(x)
+      const float2 fl = __fadd2_rn(tt, make_float2(-12582912.f, -12582912.f));
+      const float2 r = __ffma2_rn(fl, make_float2(-1.f, -1.f), x);
+      float2 q = __ffma2_rn(r, make_float2(0.05520550534f, 0.05520550534f), make_float2(0.2426139712f, 0.2426139712f));
+      q = __ffma2_rn(q, r, make_float2(0.6932547688f, 0.6932547688f));
+      q = __ffma2_rn(q, r, make_float2(0.9999276996f, 0.9999276996f));
+      pp.x = __int_as_float(__float_as_int(q.x) + (__float_as_int(tt.x) << 23));
+      pp.y = __int_as_float(__float_as_int(q.y) + (__float_as_int(tt.y) << 23));
+    } else {
+      pp = make_float2(fast_exp2(x.x), fast_exp2(x.y));
+    }
+    if (i & 1) lb = __fadd2_rn(lb, pp); else la = __fadd2_rn(la, pp);
+    pk[i] = Pack2<T>::pack(pp.x, pp.y);
+  }
+}
 
 // Per-Q-tile KV tile range [jb, je) (in units of TC5_BN keys); empty when the tile has no rows
 // or no visible keys.
@@ -66,15 +111,15 @@ __device__ __forceinline__ TileRange tc5_range(const KParams& p, int r0, int sq,
   return t;
 }
 
-template <typename T, int D, bool P_TMEM, bool HAS_ALIBI>
+template <typename T, int D, bool HAS_ALIBI>
 __global__ void __launch_bounds__(TC5_THREADS, 1)
 fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__ Tc5Maps maps) {
-  using Cfg = Tc5Cfg<D, P_TMEM>;
+  using Cfg = Tc5Cfg<D>;
   constexpr int ND = Cfg::ND, NS = Cfg::NS;
   constexpr bool IS_BF16 = IsBf16<T>::value;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B needs 1024 B
-  const uint32_t q_sm = smem_base + Cfg::OFF_Q, kv_sm = smem_base + Cfg::OFF_KV, p_sm = smem_base + Cfg::OFF_P;
+  const uint32_t q_sm = smem_base + Cfg::OFF_Q, kv_sm = smem_base + Cfg::OFF_KV;
   const uint32_t bars = smem_base + Cfg::OFF_BAR;
   const uint32_t bar_q = bars;                    // [2]
   const uint32_t bar_kv_full = bars + 16;         // [NS]
@@ -87,6 +132,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int head = blockIdx.x, bidb = blockIdx.z;
+  [[maybe_unused]] const bool trace_cta = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x & 127) == 0 || (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == TC5_MMA_WARP);
   const int m_block = p.is_causal ? (gridDim.y - 1 - blockIdx.y) : blockIdx.y;   // heavy tiles first
   const int kvh = head / p.group;
   const SeqInfo si(p, bidb);
@@ -145,16 +191,17 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
   } else if (warp == TC5_MMA_WARP) {
     setmaxnreg_dec<TC5_REGS_OTHER>();
     // =============================== MMA issuer ===============================
+    // One thread issues both tiles' chains in the order PV0(j) QK0(j+1) PV1(j) QK1(j+1): the shared
+    // in-order stream is what keeps the two softmax warpgroups in ANTI-phase (one exponentiates
+    // while the other tile's MMAs run); two independent issuers drift into phase and halve the
+    // MUFU rate each warpgroup sees.  Only one barrier wait (P_t) sits on a tile's chain: the
+    // arrival of V_j and K_{j+1} is checked before it.
     constexpr uint32_t idesc_qk = make_idesc(IS_BF16, TC5_BM, TC5_BN, false);
     constexpr uint32_t idesc_pv = make_idesc(IS_BF16, TC5_BM, D, true);
     if (elect_one()) {
       auto active = [&](int t, int j) { return t == 0 ? (j >= tr0.jb && j < tr0.je) : (j >= tr1.jb && j < tr1.je); };
-      auto slot_of = [&](int item, uint32_t& par) { par = (item / NS) & 1; return item % NS; };
       // S_t = Q_t K_j^T : A = Q (K-major, SW128), B = K (K-major, SW128); D/16 k-steps
-      auto issue_qk = [&](int t, int j) {
-        uint32_t par; const int slot = slot_of(2 * (j - j_begin), par);
-        mbar_wait(bar_kv_full + 8 * slot, par);
-        tc_fence_after();
+      auto issue_qk = [&](int t, int j, int slot, bool release) {
         const uint32_t qa = q_sm + t * Cfg::TILE_BYTES, kb = kv_sm + slot * Cfg::TILE_BYTES;
 #pragma unroll
         for (int ks = 0; ks < D / 16; ks++) {
@@ -162,44 +209,53 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
           umma_ss(tmem + Cfg::TM_S + t * 128, make_desc_sw128(qa + off, 16, 1024),
                   make_desc_sw128(kb + off, 16, 1024), idesc_qk, ks > 0);
         }
+        TC5_TRACE(2, j - 1 - j_begin, t * 8 + 5);
         umma_commit(bar_s + 8 * t);
-        const bool last_user = t == 1 || !active(1, j);
-        if (last_user) umma_commit(bar_kv_empty + 8 * slot);
-      };
-      // O_t (+)= P_t V_j : A = P (TMEM, or smem K-major), B = V (MN-major, SW128); 8 k-steps of 16 keys
-      auto issue_pv = [&](int t, int j, int jb_t, uint32_t p_par) {
-        uint32_t par; const int slot = slot_of(2 * (j - j_begin) + 1, par);
-        mbar_wait(bar_kv_full + 8 * slot, par);
-        mbar_wait(bar_p + 8 * t, p_par);
-        tc_fence_after();
-        const uint32_t vb = kv_sm + slot * Cfg::TILE_BYTES;
-#pragma unroll
-        for (int kk = 0; kk < TC5_BN / 16; kk++) {
-          const uint64_t bdesc = make_desc_sw128(vb + kk * 2048, Cfg::SUB_BYTES, 1024);
-          if constexpr (P_TMEM) {
-            umma_ts(tmem + Cfg::TM_O + t * 128, tmem + Cfg::TM_S + t * 128 + kk * 8, bdesc, idesc_pv, (j > jb_t) || kk > 0);
-          } else {
-            const uint32_t pa = p_sm + t * Cfg::P_BYTES + (kk / 4) * Cfg::SUB_BYTES + (kk % 4) * 32;
-            umma_ss(tmem + Cfg::TM_O + t * 128, make_desc_sw128(pa, 16, 1024), bdesc, idesc_pv, (j > jb_t) || kk > 0);
-          }
-        }
-        umma_commit(bar_o + 8 * t);
-        const bool last_user = t == 1 || !active(1, j);
-        if (last_user) umma_commit(bar_kv_empty + 8 * slot);
+        if (release) umma_commit(bar_kv_empty + 8 * slot);
       };
       if (act0) mbar_wait(bar_q, 0);
       if (act1) mbar_wait(bar_q + 8, 0);
-      for (int t = 0; t < 2; t++) if (active(t, j_begin)) issue_qk(t, j_begin);
+      if (j_begin < j_end) {
+        mbar_wait(bar_kv_full, 0);            // item 0 = K_{j_begin}: slot 0, first round
+        tc_fence_after();
+        const bool a0 = active(0, j_begin), a1 = active(1, j_begin);
+        if (a0) issue_qk(0, j_begin, 0, !a1);
+        if (a1) issue_qk(1, j_begin, 0, true);
+      }
       for (int j = j_begin; j < j_end; j++) {
+        const int vi = 2 * (j - j_begin) + 1, ki = vi + 1;
+        const int vslot = vi % NS, kslot = ki % NS;
+        const bool more = j + 1 < j_end;
+        TC5_TRACE(2, j - j_begin, 0);
+        mbar_wait(bar_kv_full + 8 * vslot, (vi / NS) & 1);
+        if (more) mbar_wait(bar_kv_full + 8 * kslot, (ki / NS) & 1);
+        TC5_TRACE(2, j - j_begin, 1);
+        const bool a0 = active(0, j), a1 = active(1, j);
+        const bool k0 = more && active(0, j + 1), k1 = more && active(1, j + 1);
+#pragma unroll
         for (int t = 0; t < 2; t++) {
+          const bool a = t == 0 ? a0 : a1, kq = t == 0 ? k0 : k1;
           const int jb_t = t == 0 ? tr0.jb : tr1.jb;
-          if (active(t, j)) issue_pv(t, j, jb_t, (uint32_t)((j - jb_t) & 1));
-          if (j + 1 < j_end && active(t, j + 1)) issue_qk(t, j + 1);
+          if (a) {
+            // O_t (+)= P_t V_j : A = P (TMEM), B = V (MN-major, SW128); 8 k-steps of 16 keys
+            mbar_wait(bar_p + 8 * t, (uint32_t)((j - jb_t) & 1));
+            TC5_TRACE(2, j - j_begin, t * 8 + 2);
+            tc_fence_after();
+            const uint32_t vb = kv_sm + vslot * Cfg::TILE_BYTES;
+#pragma unroll
+            for (int kk = 0; kk < TC5_BN / 16; kk++)
+              umma_ts(tmem + Cfg::TM_O + t * 128, tmem + Cfg::TM_S + t * 128 + kk * 8,
+                      make_desc_sw128(vb + kk * 2048, Cfg::SUB_BYTES, 1024), idesc_pv, (j > jb_t) || kk > 0);
+            TC5_TRACE(2, j - j_begin, t * 8 + 3);
+            umma_commit(bar_o + 8 * t);
+            if (t == 1 || !a1) umma_commit(bar_kv_empty + 8 * vslot);
+            TC5_TRACE(2, j - j_begin, t * 8 + 4);
+          }
+          if (kq) issue_qk(t, j + 1, kslot, t == 1 || !k1);
+          TC5_TRACE(2, j - j_begin, t * 8 + 6);
         }
-        if (!active(0, j) && !active(1, j)) {   // unreachable for monotone windows; keeps the ring moving
-          uint32_t par; int slot = slot_of(2 * (j - j_begin) + 1, par);
-          mbar_wait(bar_kv_full + 8 * slot, par); umma_commit(bar_kv_empty + 8 * slot);
-        }
+        if (!a0 && !a1) umma_commit(bar_kv_empty + 8 * vslot);          // unreachable for monotone windows
+        if (more && !k0 && !k1) umma_commit(bar_kv_empty + 8 * kslot);
       }
     }
     __syncwarp();
@@ -251,15 +307,6 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, int d, int hea
   return r == CUDA_SUCCESS;
 }
 
-static int g_tc5_p_mode = -1;   // -1: env not read; 0 = P through shared memory, 1 = P through TMEM
-static int tc5_p_mode() {
-  if (g_tc5_p_mode < 0) {
-    const char* e = getenv("FA_B200_TC5_P");
-    g_tc5_p_mode = (e && e[0] == 's') ? 0 : 1;
-  }
-  return g_tc5_p_mode;
-}
-
 bool tc5_supported(const KParams& p) {
   if (p.d != 64 && p.d != 128) return false;
   if (p.block_table || p.cache_batch_idx || p.seqused_k) return false;
@@ -276,12 +323,11 @@ bool tc5_supported(const KParams& p) {
   return get_encode_fn() != nullptr;
 }
 
-template <typename T, int D, bool P_TMEM, bool HAS_ALIBI>
+template <typename T, int D, bool HAS_ALIBI>
 static cudaError_t launch_tc5_t(const KParams& p, const Tc5Maps& maps, cudaStream_t stream) {
-  using Cfg = Tc5Cfg<D, P_TMEM>;
-  auto kern = fa_prefill_tc5_kernel<T, D, P_TMEM, HAS_ALIBI>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-  if (e != cudaSuccess) return e;
+  using Cfg = Tc5Cfg<D>;
+  auto kern = fa_prefill_tc5_kernel<T, D, HAS_ALIBI>;
+  FA_SET_SMEM_ONCE(kern, Cfg::SMEM);
   dim3 grid(p.h, (p.seqlen_q + 2 * TC5_BM - 1) / (2 * TC5_BM), p.b);
   kern<<<grid, TC5_THREADS, Cfg::SMEM, stream>>>(p, maps);
   return cudaGetLastError();
@@ -289,15 +335,32 @@ static cudaError_t launch_tc5_t(const KParams& p, const Tc5Maps& maps, cudaStrea
 
 template <typename T, int D>
 static cudaError_t launch_tc5_d(const KParams& p, const Tc5Maps& maps, cudaStream_t stream) {
-  const bool alibi = p.alibi_slopes != nullptr;
-  if (tc5_p_mode() == 1) {
-    return alibi ? launch_tc5_t<T, D, true, true>(p, maps, stream) : launch_tc5_t<T, D, true, false>(p, maps, stream);
-  } else {
-    return alibi ? launch_tc5_t<T, D, false, true>(p, maps, stream) : launch_tc5_t<T, D, false, false>(p, maps, stream);
-  }
+  return p.alibi_slopes != nullptr ? launch_tc5_t<T, D, true>(p, maps, stream) : launch_tc5_t<T, D, false>(p, maps, stream);
 }
 
+#ifdef FA_TC5_TRACE
+// Debug only: a device buffer for the timeline, dumped to $FA_B200_TRACE_FILE after each launch.
+static cudaError_t launch_prefill_tc5_impl(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, cudaStream_t stream);
+cudaError_t launch_prefill_tc5(const KParams& p_in, bool is_bf16, int64_t total_q, int64_t total_k, cudaStream_t stream) {
+  static long long* buf = nullptr;
+  const size_t n = 3 * 128 * 16;
+  if (!buf) cudaMalloc(&buf, n * sizeof(long long));
+  cudaMemsetAsync(buf, 0, n * sizeof(long long), stream);
+  KParams p = p_in; p.trace = buf;
+  cudaError_t e = launch_prefill_tc5_impl(p, is_bf16, total_q, total_k, stream);
+  const char* path = getenv("FA_B200_TRACE_FILE");
+  if (e == cudaSuccess && path) {
+    std::vector<long long> h(n);
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(h.data(), buf, n * sizeof(long long), cudaMemcpyDeviceToHost);
+    FILE* f = fopen(path, "wb"); if (f) { fwrite(h.data(), sizeof(long long), n, f); fclose(f); }
+  }
+  return e;
+}
+static cudaError_t launch_prefill_tc5_impl(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, cudaStream_t stream) {
+#else
 cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, cudaStream_t stream) {
+#endif
   Tc5Maps maps;
   const bool varlen = p.cu_seqlens_q != nullptr;
   const int64_t q_rows = varlen ? total_q : p.seqlen_q, k_rows = varlen ? total_k : p.seqlen_k;

@@ -189,8 +189,7 @@ template <typename T, int D>
 static cudaError_t launch_tile_t(const KParams& p, cudaStream_t stream) {
   using Cfg = TileCfg<D>;
   auto kern = fa_tile_kernel<T, D>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM);
-  if (e != cudaSuccess) return e;
+  FA_SET_SMEM_ONCE(kern, Cfg::SMEM);
   const int m_blocks = (p.seqlen_q + Cfg::BM - 1) / Cfg::BM;
   dim3 grid(m_blocks * p.num_splits, p.h, p.b);
   kern<<<grid, 128, Cfg::SMEM, stream>>>(p);
