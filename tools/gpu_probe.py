@@ -23,7 +23,7 @@ K_TC5, K_TILE, K_DEC = 1, 2, 3
 
 def C(name, kern, kind="dense", **kw):
     d = dict(name=name, kern=kern, kind=kind, b=2, sq=256, sk=256, h=4, hk=4, d=128, dtype="bf16",
-             causal=False, window=(-1, -1), alibi=False, pmode="t", page=0, splits=0, seed=0)
+             causal=False, window=(-1, -1), alibi=False, pmode="t", page=0, splits=0, seed=0, mixed=0.0, poison=False)
     d.update(kw)
     return d
 
@@ -65,6 +65,17 @@ CASES += [
     C("dec_alibi", K_DEC, kind="kvcache", b=2, sq=1, sk=300, h=4, hk=4, alibi=True, causal=True),
     C("dec_local", K_DEC, kind="kvcache", b=2, sq=2, sk=500, h=4, hk=2, window=(64, 0)),
     C("dec_varlen_paged", K_DEC, kind="varlen", b=6, sq=1, sk=800, page=16, h=8, hk=2, causal=True),
+    # paged K/V through the tcgen05 prefill kernel (forced), then auto dispatch on mixed prefill+decode batches
+    C("tc5_varlen_paged16", K_TC5, kind="varlen", b=3, sq=300, sk=700, page=16, h=8, hk=2, causal=True, poison=True),
+    C("tc5_varlen_paged64_d64", K_TC5, kind="varlen", b=3, sq=200, sk=500, page=64, d=64, h=4, hk=4, dtype="fp16", poison=True),
+    C("tc5_varlen_paged128_local", K_TC5, kind="varlen", b=2, sq=400, sk=600, page=128, h=4, hk=2, window=(100, 20), poison=True),
+    C("tc5_varlen_paged256", K_TC5, kind="varlen", b=2, sq=300, sk=1000, page=256, h=4, hk=1, causal=True, poison=True),
+    C("tc5_kvcache_paged16", K_TC5, kind="kvcache", b=2, sq=200, sk=900, page=16, h=8, hk=2, causal=True),
+    C("tc5_kvcache_paged32_alibi", K_TC5, kind="kvcache", b=2, sq=150, sk=500, page=32, h=4, hk=4, causal=True, alibi=True),
+    C("mixed_paged16", 0, kind="varlen", expect=K_TC5, b=8, sq=400, sk=900, page=16, h=8, hk=2, causal=True, mixed=0.6, poison=True),
+    C("mixed_paged16_g8", 0, kind="varlen", expect=K_TC5, b=6, sq=300, sk=700, page=16, h=16, hk=2, causal=True, mixed=0.5, poison=True),
+    C("mixed_dense_varlen", 0, kind="varlen", expect=K_TC5, b=7, sq=300, sk=600, h=8, hk=2, causal=True, mixed=0.5),
+    C("mixed_paged_d64", 0, kind="varlen", expect=K_TC5, b=5, sq=260, sk=520, page=32, d=64, h=8, hk=8, causal=True, mixed=0.4, poison=True),
 ]
 
 
@@ -89,6 +100,9 @@ def run_case(spec):
         r = dict(err=(out.float() - ref32.float()).abs().max().item(),
                  err_pt=(out_pt.float() - ref32.float()).abs().max().item(),
                  nan=bool(torch.isnan(out.float()).any().item()))
+        e = (out.float() - ref32.float()).abs()
+        r["err_at"] = [int(x) for x in torch.unravel_index(e.argmax(), e.shape)]
+        r["n_bad"] = int((e > 4 * r["err_pt"] + 1e-3).sum().item())
         if out_refk is not None:
             r["err_refk"] = (out_refk.float() - ref32.float()).abs().max().item()
             r["vs_refk"] = (out.float() - out_refk.float()).abs().max().item()
@@ -120,6 +134,11 @@ def run_case(spec):
         else:
             lens_q = torch.randint(max(1, sq // 3), sq + 1, (b,), generator=g)
         lens_k = lens_q.clone() if (sq == sk and sq > 1) else torch.randint(max(1, sk // 3), sk + 1, (b,), generator=g)
+        if spec["mixed"] > 0:     # some sequences are single-token decodes (vLLM chunked prefill batches)
+            is_dec = torch.rand(b, generator=g) < spec["mixed"]
+            is_dec[0], is_dec[-1] = False, True
+            lens_q = torch.where(is_dec, torch.ones_like(lens_q), lens_q)
+            lens_q = torch.minimum(lens_q, lens_k)
         cu_q = torch.zeros(b + 1, dtype=torch.int32); cu_q[1:] = lens_q.cumsum(0)
         cu_k = torch.zeros(b + 1, dtype=torch.int32); cu_k[1:] = lens_k.cumsum(0)
         q = torch.randn(int(cu_q[-1]), h, d, device=dev, dtype=dt)
@@ -135,6 +154,15 @@ def run_case(spec):
             kk = torch.randn(nblocks, page, hk, d, device=dev, dtype=dt)
             vv = torch.randn(nblocks, page, hk, d, device=dev, dtype=dt)
             bt = torch.randperm(nblocks, generator=g).to(torch.int32).view(b, -1).to(dev)
+            if spec["poison"]:    # rows no sequence owns hold NaN: they must never reach the output
+                own = torch.zeros(nblocks * page, dtype=torch.bool)
+                for i in range(b):
+                    for r0 in range(0, int(lens_k[i]), page):
+                        blk = int(bt[i, r0 // page])
+                        own[blk * page + torch.arange(min(page, int(lens_k[i]) - r0))] = True
+                own = own.view(nblocks, page, 1, 1).to(dev)
+                kk = torch.where(own, kk, torch.full_like(kk, float("nan")))
+                vv = torch.where(own, vv, torch.full_like(vv, float("nan")))
             kg, vg = orc.gather_paged(kk, bt), orc.gather_paged(vv, bt)
             kd = torch.cat([kg[i, :int(lens_k[i])] for i in range(b)])
             vd = torch.cat([vg[i, :int(lens_k[i])] for i in range(b)])
@@ -148,6 +176,7 @@ def run_case(spec):
         if refk and slopes is None:
             ork = _util.ref_kernel_varlen(q, kk, vv, cq, ck, max_q, max_k, causal, window, bt)[0]
         res.update(errs(out, ref32, out_pt, ork))
+        res["lens_q"], res["lens_k"] = lens_q.tolist(), lens_k.tolist()
         lerr = 0.0
         for i in range(b):
             n = int(lens_q[i])

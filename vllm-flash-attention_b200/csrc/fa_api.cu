@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <climits>
 #include <cstring>
 #include <vector>
 #include "fa_b200.h"
@@ -64,6 +65,7 @@ struct Plan {
   int num_splits;
   size_t ws_bytes;
   bool is_bf16;
+  int decode_rows;   // > 0: mixed varlen batch — sequences with at most this many packed rows go to the decode kernel
 };
 
 // Validation + normalisation shared by the three ops.  Mirrors the checks of mha_fwd /
@@ -112,6 +114,7 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   k.cache_batch_idx = a->cache_batch_idx;
   k.seqlen_knew = a->seqlen_knew;   // rows already appended by fa_b200_append_kv
   k.lse_seq_stride = a->seqlen_q;
+  k.min_rows = 0; k.max_rows = INT_MAX;
   k.partial = 0;
   if (a->partial_out) {
     FA_CHECK(op == OP_KVCACHE, "partial_out is only valid for fwd_kvcache");
@@ -143,10 +146,16 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   const int rows = a->seqlen_q * k.group;     // packed rows per (sequence, kv head)
   int kernel = a->force_kernel;
   k.num_splits = 1;
+  pl->decode_rows = 0;
   if (kernel == FA_KERNEL_NONE) {
     if (decode_supported(a->d, rows)) kernel = FA_KERNEL_DECODE;
-    else if (!k.partial && tc5_supported(k)) kernel = FA_KERNEL_TC5_PREFILL;
-    else kernel = FA_KERNEL_TILE;
+    else if (!k.partial && tc5_supported(k)) {
+      kernel = FA_KERNEL_TC5_PREFILL;
+      // A varlen batch may mix prompts with single-token (or few-token) sequences — vLLM's chunked
+      // prefill.  Those would waste a 256-row tile per head, so they are routed to the decode
+      // kernel (one CTA per KV head, K/V read once per group) by a second launch over the same batch.
+      if (op == OP_VARLEN && decode_supported(a->d, k.group)) pl->decode_rows = 32;
+    } else kernel = FA_KERNEL_TILE;
   }
   if (kernel == FA_KERNEL_DECODE) FA_CHECK(decode_supported(a->d, rows), "decode kernel: d/rows not supported");
   if (kernel == FA_KERNEL_TC5_PREFILL) FA_CHECK(!k.partial && tc5_supported(k), "tcgen05 prefill kernel: shape/layout not supported");
@@ -203,11 +212,19 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
   switch (pl.kernel) {
     case FA_KERNEL_DECODE: e = launch_decode(k, pl.is_bf16, stream); break;
     case FA_KERNEL_TILE: e = launch_tile(k, pl.is_bf16, stream); break;
-    case FA_KERNEL_TC5_PREFILL: e = launch_prefill_tc5(k, pl.is_bf16, a->total_q, a->total_k, stream); break;
+    case FA_KERNEL_TC5_PREFILL:
+      if (pl.decode_rows > 0) k.min_rows = pl.decode_rows + 1;
+      e = launch_prefill_tc5(k, pl.is_bf16, a->total_q, a->total_k, stream);
+      if (e == cudaSuccess && pl.decode_rows > 0) {
+        k.min_rows = 0; k.max_rows = pl.decode_rows;
+        e = launch_decode(k, pl.is_bf16, stream);
+        a->launches = 1;
+      }
+      break;
     default: return fail(FA_ERR_INVALID, "unknown kernel id %d", pl.kernel);
   }
   if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in attention kernel launch: %s", cudaGetErrorString(e));
-  a->launches = 1;
+  a->launches += 1;
   if (pl.num_splits > 1) {
     CombineParams c;
     c.o_part = k.o_accum; c.lse_part = k.lse_accum; c.o = a->o; c.lse = a->softmax_lse;

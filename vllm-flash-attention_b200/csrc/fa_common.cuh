@@ -34,6 +34,7 @@ struct KParams {
   int seqlen_knew;                              // keys appended this call (already in cache)
   int num_splits;
   int lse_seq_stride;                           // seqlen_q used for lse/accum row indexing
+  int min_rows, max_rows;                        // serve only sequences with min_rows <= seqlen_q*group <= max_rows (mixed batches)
   long long* trace;                             // FA_TC5_TRACE builds only: per-event clock64 stamps of one CTA
   int partial;                                  // write fp32 partials (o_accum/lse_accum, -inf for empty rows) even with 1 split
 };

@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
   const SeqInfo si(p, bidb);
   const int sq = si.sq, sk = si.sk;
   const int R = sq * g;  // live packed rows: r = qpos*g + head_in_group
-  if (sq <= 0) return;
+  if (sq <= 0 || R < p.min_rows || R > p.max_rows) return;   // mixed batch: longer sequences belong to the prefill kernel
 
   // ---- KV chunk range of this CTA ----
   const RowWindow w_first = row_window(p, 0, sq, sk), w_last = row_window(p, sq - 1, sq, sk);
@@ -309,6 +309,7 @@ bool decode_supported(int d, int rows) {
 
 cudaError_t launch_decode(const KParams& p, bool is_bf16, cudaStream_t stream) {
   int rows = p.seqlen_q * p.group;
+  if (rows > p.max_rows) rows = p.max_rows;   // mixed batch: longer sequences are skipped by the kernel
   int mt = rows <= 16 ? 1 : 2;
   return is_bf16 ? launch_decode_d<__nv_bfloat16>(p, mt, stream) : launch_decode_d<__half>(p, mt, stream);
 }

@@ -50,7 +50,7 @@ template <int D> struct Tc5Cfg {
   static constexpr int ND = D / 64;                         // 64-element (128 B) sub-tiles per row
   static constexpr int SUB_BYTES = 128 * 128;               // 128 rows x 128 B
   static constexpr int TILE_BYTES = ND * SUB_BYTES;         // a Q / K / V tile
-  static constexpr int NS = D == 128 ? 5 : 8;
+  static constexpr int NS = D == 128 ? 4 : 8;
   static constexpr int OFF_Q = 0;
   static constexpr int OFF_KV = 2 * TILE_BYTES;
   static constexpr int OFF_BAR = OFF_KV + NS * TILE_BYTES;
@@ -111,7 +111,7 @@ __device__ __forceinline__ TileRange tc5_range(const KParams& p, int r0, int sq,
   return t;
 }
 
-template <typename T, int D, bool HAS_ALIBI>
+template <typename T, int D, bool HAS_ALIBI, bool PAGED>
 __global__ void __launch_bounds__(TC5_THREADS, 1)
 fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__ Tc5Maps maps) {
   using Cfg = Tc5Cfg<D>;
@@ -138,7 +138,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
   const SeqInfo si(p, bidb);
   const int sq = si.sq, sk = si.sk;
   const int m0 = m_block * 2 * TC5_BM;
-  if (m0 >= sq) return;
+  if (m0 >= sq || sq * p.group < p.min_rows || sq * p.group > p.max_rows) return;
   const int q_row0 = p.cu_seqlens_q ? p.cu_seqlens_q[bidb] : 0;     // row coordinate bases (varlen)
   const int k_row0 = p.cu_seqlens_k ? p.cu_seqlens_k[bidb] : 0;
   const int bcoord = p.cu_seqlens_q ? 0 : bidb;
@@ -175,19 +175,74 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
           tma_load_4d(q_sm + t * Cfg::TILE_BYTES + c * Cfg::SUB_BYTES, &maps.q, bar_q + 8 * t,
                       c * 64, head, q_row0 + m0 + t * TC5_BM, bcoord);
       }
-      int item = 0;
-      for (int j = j_begin; j < j_end; j++) {
-        for (int kv = 0; kv < 2; kv++, item++) {
-          const int slot = item % NS, round = item / NS;
-          mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
-          mbar_expect_tx(bar_kv_full + 8 * slot, Cfg::TILE_BYTES);
-          for (int c = 0; c < ND; c++)
-            tma_load_4d(kv_sm + slot * Cfg::TILE_BYTES + c * Cfg::SUB_BYTES, kv == 0 ? &maps.k : &maps.v,
-                        bar_kv_full + 8 * slot, c * 64, kvh, k_row0 + j * TC5_BN, p.cu_seqlens_k ? 0 : bidb);
+      if constexpr (!PAGED) {
+        int item = 0;
+        for (int j = j_begin; j < j_end; j++) {
+          for (int kv = 0; kv < 2; kv++, item++) {
+            const int slot = item % NS, round = item / NS;
+            mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
+            mbar_expect_tx(bar_kv_full + 8 * slot, Cfg::TILE_BYTES);
+            for (int c = 0; c < ND; c++)
+              tma_load_4d(kv_sm + slot * Cfg::TILE_BYTES + c * Cfg::SUB_BYTES, kv == 0 ? &maps.k : &maps.v,
+                          bar_kv_full + 8 * slot, c * 64, kvh, k_row0 + j * TC5_BN, p.cu_seqlens_k ? 0 : bidb);
+          }
         }
       }
     }
     __syncwarp();
+    if constexpr (PAGED) {
+      // Paged K/V (reference src/utils.h:297-315, kernel_traits.h:136-144): a 128-key tile is
+      // 128/box pages (or a slice of one big page); lane L looks up the block id of box L in the
+      // block table and issues that box's TMA loads itself, so the table indirection costs one
+      // coalesced load per tile.  The tensor maps are (d, heads, page_row, block).  The V tile that
+      // contains the end of the sequence is special: rows >= seqlen_k hold whatever the pool holds
+      // (possibly NaN) and 0 * NaN would poison P.V, so its boxes that reach past the end are copied
+      // by hand (valid rows) / zero-filled (the rest) in the 128-B swizzle TMA would have used.
+      const int page = p.page_block_size;
+      const int box_rows = min(page, TC5_BN), nbox = TC5_BN / box_rows;
+      const int* table = p.block_table + (int64_t)bidb * p.block_table_batch_stride;
+      int item = 0;
+      for (int j = j_begin; j < j_end; j++) {
+        const int row0 = j * TC5_BN;
+        const int valid = min(TC5_BN, sk - row0);                    // rows of this tile inside the sequence (>= 1)
+        for (int kv = 0; kv < 2; kv++, item++) {
+          const int slot = item % NS, round = item / NS;
+          if (lane == 0) mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
+          __syncwarp();
+          const uint32_t dst = kv_sm + slot * Cfg::TILE_BYTES, bar = bar_kv_full + 8 * slot;
+          const bool tail = kv == 1 && valid < TC5_BN;
+          const int n_tma_boxes = tail ? valid / box_rows : nbox;      // boxes entirely inside the sequence
+          if (tail) {
+            const T* vbase = reinterpret_cast<const T*>(p.v) + (int64_t)kvh * p.v_head_stride;
+            const int r_begin = n_tma_boxes * box_rows;
+            for (int idx = lane; idx < (TC5_BN - r_begin) * ND * 8; idx += 32) {
+              const int ch = idx & 7, c = (idx >> 3) % ND, r = r_begin + (idx >> 3) / ND;
+              uint4 val = make_uint4(0, 0, 0, 0);
+              if (r < valid) {
+                const int g = row0 + r, pg = g / page;
+                const int blk = table[min(pg, p.max_blocks_per_seq - 1)];
+                val = *reinterpret_cast<const uint4*>(vbase + (int64_t)blk * p.v_batch_stride +
+                                                      (int64_t)(g - pg * page) * p.v_row_stride + c * 64 + ch * 8);
+              }
+              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + c * Cfg::SUB_BYTES + r * 128 + ((ch ^ (r & 7)) << 4)),
+                           "r"(val.x), "r"(val.y), "r"(val.z), "r"(val.w) : "memory");
+            }
+            fence_proxy_async_smem();
+          }
+          __syncwarp();
+          if (lane == 0) mbar_expect_tx(bar, (uint32_t)(n_tma_boxes * box_rows * 128 * ND));
+          __syncwarp();
+          if (lane < n_tma_boxes) {
+            const int g = row0 + lane * box_rows, pg = g / page;
+            const int blk = table[min(pg, p.max_blocks_per_seq - 1)];
+            for (int c = 0; c < ND; c++)
+              tma_load_4d(dst + c * Cfg::SUB_BYTES + lane * box_rows * 128, kv == 0 ? &maps.k : &maps.v, bar,
+                          c * 64, kvh, g - pg * page, blk);
+          }
+        }
+      }
+      __syncwarp();
+    }
   } else if (warp == TC5_MMA_WARP) {
     setmaxnreg_dec<TC5_REGS_OTHER>();
     // =============================== MMA issuer ===============================
@@ -291,15 +346,15 @@ static EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-// 4-D map over (d, heads, rows, batch) with a 64 x 1 x 128 x 1 box and 128-byte swizzle.
-static bool make_map(CUtensorMap* m, const void* base, bool bf16, int d, int heads, int64_t rows, int batch,
+// 4-D map over (d, heads, rows, batch) with a 64 x 1 x box_rows x 1 box and 128-byte swizzle.
+static bool make_map(CUtensorMap* m, const void* base, bool bf16, int box_rows, int d, int heads, int64_t rows, int batch,
                      int64_t head_stride, int64_t row_stride, int64_t batch_stride) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return false;
   cuuint64_t dims[4] = {(cuuint64_t)d, (cuuint64_t)heads, (cuuint64_t)rows, (cuuint64_t)batch};
   cuuint64_t strides[3] = {(cuuint64_t)head_stride * 2, (cuuint64_t)row_stride * 2,
                            (cuuint64_t)(batch > 1 ? batch_stride : row_stride * rows) * 2};
-  cuuint32_t box[4] = {64, 1, 128, 1};
+  cuuint32_t box[4] = {64, 1, (cuuint32_t)box_rows, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -309,10 +364,16 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, int d, int hea
 
 bool tc5_supported(const KParams& p) {
   if (p.d != 64 && p.d != 128) return false;
-  if (p.block_table || p.cache_batch_idx || p.seqused_k) return false;
-  if (p.cu_seqlens_k && !p.is_seqlens_k_cumulative) return false;
-  if ((p.cu_seqlens_q == nullptr) != (p.cu_seqlens_k == nullptr)) return false;
+  if (p.cache_batch_idx || p.seqused_k) return false;
   if (p.num_splits > 1) return false;
+  if (p.block_table) {
+    // paged K/V: a 128-key tile must be a whole number of pages, or a page a whole number of tiles
+    const int pg = p.page_block_size;
+    if (pg <= 0 || !(pg % TC5_BN == 0 || TC5_BN % pg == 0) || p.num_blocks <= 0) return false;
+  } else {
+    if (p.cu_seqlens_k && !p.is_seqlens_k_cumulative) return false;
+    if ((p.cu_seqlens_q == nullptr) != (p.cu_seqlens_k == nullptr)) return false;
+  }
   // TMA: 16-byte aligned base and strides
   auto al = [](const void* x) { return (reinterpret_cast<uintptr_t>(x) & 15) == 0; };
   if (!al(p.q) || !al(p.k) || !al(p.v) || !al(p.o)) return false;
@@ -323,10 +384,10 @@ bool tc5_supported(const KParams& p) {
   return get_encode_fn() != nullptr;
 }
 
-template <typename T, int D, bool HAS_ALIBI>
+template <typename T, int D, bool HAS_ALIBI, bool PAGED>
 static cudaError_t launch_tc5_t(const KParams& p, const Tc5Maps& maps, cudaStream_t stream) {
   using Cfg = Tc5Cfg<D>;
-  auto kern = fa_prefill_tc5_kernel<T, D, HAS_ALIBI>;
+  auto kern = fa_prefill_tc5_kernel<T, D, HAS_ALIBI, PAGED>;
   FA_SET_SMEM_ONCE(kern, Cfg::SMEM);
   dim3 grid(p.h, (p.seqlen_q + 2 * TC5_BM - 1) / (2 * TC5_BM), p.b);
   kern<<<grid, TC5_THREADS, Cfg::SMEM, stream>>>(p, maps);
@@ -335,7 +396,9 @@ static cudaError_t launch_tc5_t(const KParams& p, const Tc5Maps& maps, cudaStrea
 
 template <typename T, int D>
 static cudaError_t launch_tc5_d(const KParams& p, const Tc5Maps& maps, cudaStream_t stream) {
-  return p.alibi_slopes != nullptr ? launch_tc5_t<T, D, true>(p, maps, stream) : launch_tc5_t<T, D, false>(p, maps, stream);
+  const bool alibi = p.alibi_slopes != nullptr;
+  if (p.block_table) return alibi ? launch_tc5_t<T, D, true, true>(p, maps, stream) : launch_tc5_t<T, D, false, true>(p, maps, stream);
+  return alibi ? launch_tc5_t<T, D, true, false>(p, maps, stream) : launch_tc5_t<T, D, false, false>(p, maps, stream);
 }
 
 #ifdef FA_TC5_TRACE
@@ -363,12 +426,19 @@ cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, 
 #endif
   Tc5Maps maps;
   const bool varlen = p.cu_seqlens_q != nullptr;
-  const int64_t q_rows = varlen ? total_q : p.seqlen_q, k_rows = varlen ? total_k : p.seqlen_k;
-  const int nb = varlen ? 1 : p.b;
-  if (!make_map(&maps.q, p.q, is_bf16, p.d, p.h, q_rows, nb, p.q_head_stride, p.q_row_stride, p.q_batch_stride) ||
-      !make_map(&maps.k, p.k, is_bf16, p.d, p.h_k, k_rows, nb, p.k_head_stride, p.k_row_stride, p.k_batch_stride) ||
-      !make_map(&maps.v, p.v, is_bf16, p.d, p.h_k, k_rows, nb, p.v_head_stride, p.v_row_stride, p.v_batch_stride))
-    return cudaErrorInvalidValue;
+  const int64_t q_rows = varlen ? total_q : p.seqlen_q;
+  bool ok = make_map(&maps.q, p.q, is_bf16, TC5_BM, p.d, p.h, q_rows, varlen ? 1 : p.b, p.q_head_stride, p.q_row_stride, p.q_batch_stride);
+  if (p.block_table) {   // (d, heads, row in page, block)
+    const int box = p.page_block_size < TC5_BN ? p.page_block_size : TC5_BN;
+    ok = ok && make_map(&maps.k, p.k, is_bf16, box, p.d, p.h_k, p.page_block_size, p.num_blocks, p.k_head_stride, p.k_row_stride, p.k_batch_stride) &&
+         make_map(&maps.v, p.v, is_bf16, box, p.d, p.h_k, p.page_block_size, p.num_blocks, p.v_head_stride, p.v_row_stride, p.v_batch_stride);
+  } else {
+    const bool kvarlen = p.cu_seqlens_k != nullptr;
+    const int64_t k_rows = kvarlen ? total_k : p.seqlen_k;
+    ok = ok && make_map(&maps.k, p.k, is_bf16, TC5_BN, p.d, p.h_k, k_rows, kvarlen ? 1 : p.b, p.k_head_stride, p.k_row_stride, p.k_batch_stride) &&
+         make_map(&maps.v, p.v, is_bf16, TC5_BN, p.d, p.h_k, k_rows, kvarlen ? 1 : p.b, p.v_head_stride, p.v_row_stride, p.v_batch_stride);
+  }
+  if (!ok) return cudaErrorInvalidValue;
   if (is_bf16) return p.d == 64 ? launch_tc5_d<__nv_bfloat16, 64>(p, maps, stream) : launch_tc5_d<__nv_bfloat16, 128>(p, maps, stream);
   return p.d == 64 ? launch_tc5_d<__half, 64>(p, maps, stream) : launch_tc5_d<__half, 128>(p, maps, stream);
 }

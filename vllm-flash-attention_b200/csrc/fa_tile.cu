@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(128) fa_tile_kernel(const __grid_constant__ KP
   const SeqInfo si(p, bidb);
   const int sq = si.sq, sk = si.sk;
   const int m0 = m_block * BM;
-  if (m0 >= sq) return;
+  if (m0 >= sq || sq * p.group < p.min_rows || sq * p.group > p.max_rows) return;
   const int m_last = min(m0 + BM, sq) - 1;
 
   // visible KV tiles for this row block, then this split's share
