@@ -43,6 +43,9 @@ def main():
     for it in range(a.first, a.first + a.count):
         for wg in (0, 1):
             e = [ev(wg, it, i) - t00 for i in range(6)]
+            x = [ev(wg, it, i) for i in (6, 7, 8)]
+            if x[0]:
+                print(f"        WG{wg} unit end after it {it}: PV(last) done @{x[0]-t00}, epilogue stores +{x[1]-x[0]}, next unit read +{x[2]-x[1]}")
             print(f"it {it:3d} WG{wg}: wait@{e[0]:7d} S_ready +{e[1]-e[0]:5d} ld1 +{e[2]-e[1]:4d} max +{e[3]-e[2]:4d} "
                   f"exp_half +{e[4]-e[3]:5d} P_pub +{e[5]-e[4]:5d}  | iter total {e[5]-e[0]:5d}  S_ready@{e[1]:7d} P_hi@{e[5]:7d}")
         m = [ev(2, it, i) - t00 for i in range(16)]

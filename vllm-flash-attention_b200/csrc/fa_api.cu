@@ -65,6 +65,7 @@ struct Plan {
   int num_splits;
   size_t ws_bytes;
   bool is_bf16;
+  int num_sms;
   int decode_rows;   // > 0: mixed varlen batch — sequences with at most this many packed rows go to the decode kernel
 };
 
@@ -182,7 +183,12 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
     FA_CHECK(splits <= 128, "num_splits > 128 not supported");                         // :217
   }
   k.num_splits = pl->num_splits = splits;
+  pl->num_sms = num_sms;
   pl->ws_bytes = splits > 1 ? (size_t)splits * a->b * a->h * std::max(a->seqlen_q, 1) * (a->d + 1) * sizeof(float) : 0;
+  if (kernel == FA_KERNEL_TC5_PREFILL) {
+    if (op == OP_VARLEN) FA_CHECK(a->total_q > 0, "total_q (rows of q) must be given for varlen_fwd");
+    pl->ws_bytes = tc5_workspace_bytes(k, a->total_q, num_sms);    // cost-sorted work list of the persistent kernel
+  }
   return FA_OK;
 }
 
@@ -214,11 +220,19 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
     case FA_KERNEL_TILE: e = launch_tile(k, pl.is_bf16, stream); break;
     case FA_KERNEL_TC5_PREFILL:
       if (pl.decode_rows > 0) k.min_rows = pl.decode_rows + 1;
-      e = launch_prefill_tc5(k, pl.is_bf16, a->total_q, a->total_k, stream);
+      if (pl.ws_bytes) {
+        if (a->workspace == nullptr || a->workspace_bytes < pl.ws_bytes)
+          return fail(FA_ERR_WORKSPACE, "work-list workspace too small: need %zu bytes, got %zu", pl.ws_bytes, a->workspace_bytes);
+        if ((reinterpret_cast<uintptr_t>(a->workspace) & 7) != 0) return fail(FA_ERR_INVALID, "workspace must be 8-byte aligned");
+        k.work_header = reinterpret_cast<int*>(a->workspace);
+        k.work_items = reinterpret_cast<int2*>(reinterpret_cast<char*>(a->workspace) + 16);
+      }
+      e = launch_prefill_tc5(k, pl.is_bf16, a->total_q, a->total_k, pl.num_sms, stream);
+      a->launches = pl.ws_bytes ? 1 : 0;
       if (e == cudaSuccess && pl.decode_rows > 0) {
         k.min_rows = 0; k.max_rows = pl.decode_rows;
         e = launch_decode(k, pl.is_bf16, stream);
-        a->launches = 1;
+        a->launches += 1;
       }
       break;
     default: return fail(FA_ERR_INVALID, "unknown kernel id %d", pl.kernel);

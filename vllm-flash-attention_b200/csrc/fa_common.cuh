@@ -35,6 +35,7 @@ struct KParams {
   int num_splits;
   int lse_seq_stride;                           // seqlen_q used for lse/accum row indexing
   int min_rows, max_rows;                        // serve only sequences with min_rows <= seqlen_q*group <= max_rows (mixed batches)
+  int2* work_items; int* work_header;           // tcgen05 prefill: cost-sorted (sequence, m_block) list + {draw counter, count}; NULL = static order
   long long* trace;                             // FA_TC5_TRACE builds only: per-event clock64 stamps of one CTA
   int partial;                                  // write fp32 partials (o_accum/lse_accum, -inf for empty rows) even with 1 split
 };

@@ -62,7 +62,8 @@ cudaError_t launch_append(const AppendParams& a, bool is_bf16, cudaStream_t stre
 
 // fa_prefill_tc5.cu — tcgen05/TMA/TMEM prefill kernel, d in {64,128}.
 bool tc5_supported(const KParams& p);
-cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k,
+cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, int num_sms,
                                cudaStream_t stream);
+size_t tc5_workspace_bytes(const KParams& p, int64_t total_q, int num_sms);
 
 }  // namespace fa

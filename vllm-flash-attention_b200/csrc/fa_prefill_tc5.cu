@@ -9,11 +9,12 @@
 // One deliberate difference: O is rescaled lazily (only when the running max grows by more than
 // 2^8), which changes the reference max `m` used inside exp2 but not the normalised result.
 //
-// CTA = 256 query rows of one (sequence, head) as two 128-row tiles that ping-pong through the
+// Persistent CTAs (one per SM) draw work units from a cost-sorted list (tc5_schedule_kernel).
+// Work unit = 256 query rows of one (sequence, head) as two 128-row tiles that ping-pong through the
 // tensor core, 12 warps (warps 10-11 idle: setmaxnreg moves registers by whole warpgroups):
 //   warps 0-3  softmax warpgroup of Q tile 0   (TMEM lanes 0..127 = rows; thread = row)
 //   warps 4-7  softmax warpgroup of Q tile 1
-//   warp  8    TMA producer (Q tiles once, then K_j, V_j through an NS-slot ring)
+//   warp  8    scheduler + TMA producer (work mailbox, Q tiles, then K_j, V_j through an NS-slot ring)
 //   warp  9    MMA issuer (one elected lane) + TMEM allocation
 // TMEM (512 columns): S0 [0,128) S1 [128,256) O0 [256,256+D) O1 [384,384+D); bf16 P_t overwrites
 // the first 64 columns of S_t (all of S_t is in registers by then).
@@ -21,6 +22,7 @@
 // S0(j+1) the tensor core runs PV1(j) and QK1(j+1).
 #include "fa_common.cuh"
 #include "fa_sm100.cuh"
+#include <algorithm>
 #include <type_traits>
 #include <vector>
 #include "fa_launch.h"
@@ -38,8 +40,10 @@ using namespace sm100;
 
 constexpr int TC5_BM = 128;        // rows per Q tile (UMMA M)
 constexpr int TC5_BN = 128;        // keys per KV tile (UMMA N for QK^T)
-constexpr int TC5_THREADS = 384;       // 3 warpgroups; warps 10-11 only donate registers
-constexpr int TC5_REGS_SOFTMAX = 224, TC5_REGS_OTHER = 56;   // 256*224 + 128*56 = 384*168
+constexpr int TC5_THREADS = 384;       // 3 warpgroups; warps 10-11 idle (setmaxnreg works on whole warpgroups)
+// Registers live in the 4 SM sub-partitions (16K each): a sub-partition holds softmax warps w and w+4 plus
+// one of warps 8-11, so 2*224 + 56 (= 3*168, the launch allocation) is the most the split can give.
+constexpr int TC5_REGS_SOFTMAX = 224, TC5_REGS_OTHER = 56;
 constexpr int TC5_PRODUCER_WARP = 8, TC5_MMA_WARP = 9;
 
 struct Tc5Maps { CUtensorMap q, k, v; };
@@ -54,8 +58,10 @@ template <int D> struct Tc5Cfg {
   static constexpr int OFF_Q = 0;
   static constexpr int OFF_KV = 2 * TILE_BYTES;
   static constexpr int OFF_BAR = OFF_KV + NS * TILE_BYTES;
-  static constexpr int NUM_BARS = 2 /*q*/ + 2 * NS + 2 /*s*/ + 2 /*p*/ + 2 /*o*/;
-  static constexpr int SMEM = OFF_BAR + NUM_BARS * 8 + 16 + 1024;   // +1024: manual alignment
+  static constexpr int NUM_BARS = 4 /*q full,empty*/ + 2 * NS + 2 /*s*/ + 2 /*p*/ + 2 /*o*/ + 4 /*mailbox full,empty*/;
+  static constexpr int OFF_MBOX = OFF_BAR + NUM_BARS * 8 + 16;      // after the TMEM base slot; 2 x 32 B
+  static constexpr int OFF_STAGE = OFF_MBOX + 64;                   // epilogue staging: 8 softmax warps x 4 KB
+  static constexpr int SMEM = OFF_STAGE + 8 * 4096 + 1024;          // +1024: manual alignment
   static constexpr int TM_S = 0, TM_O = 256;                // TMEM column bases; tile t adds t*128
 };
 
@@ -111,6 +117,15 @@ __device__ __forceinline__ TileRange tc5_range(const KParams& p, int r0, int sq,
   return t;
 }
 
+// One unit of work = 256 query rows (two 128-row tiles) of one (sequence, head).  The producer
+// warp decodes it and publishes it to the other roles through a 2-deep shared-memory mailbox.
+struct Tc5Work { int valid, head, bidb, m_block, sq, sk, q_row0, k_row0; };
+
+__device__ __forceinline__ void tc5_read_work(const uint8_t* mbox, Tc5Work& w) {
+  const int4 a = *reinterpret_cast<const int4*>(mbox), b = *reinterpret_cast<const int4*>(mbox + 16);
+  w.valid = a.x; w.head = a.y; w.bidb = a.z; w.m_block = a.w; w.sq = b.x; w.sk = b.y; w.q_row0 = b.z; w.k_row0 = b.w;
+}
+
 template <typename T, int D, bool HAS_ALIBI, bool PAGED>
 __global__ void __launch_bounds__(TC5_THREADS, 1)
 fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__ Tc5Maps maps) {
@@ -119,41 +134,34 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
   constexpr bool IS_BF16 = IsBf16<T>::value;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;   // SWIZZLE_128B needs 1024 B
+  uint8_t* smem_al = smem_raw + (smem_base - smem_u32(smem_raw));
   const uint32_t q_sm = smem_base + Cfg::OFF_Q, kv_sm = smem_base + Cfg::OFF_KV;
   const uint32_t bars = smem_base + Cfg::OFF_BAR;
-  const uint32_t bar_q = bars;                    // [2]
-  const uint32_t bar_kv_full = bars + 16;         // [NS]
+  const uint32_t bar_q = bars;                    // [2] Q_t landed
+  const uint32_t bar_q_empty = bars + 16;         // [2] last QK_t of the work unit complete
+  const uint32_t bar_kv_full = bars + 32;         // [NS]
   const uint32_t bar_kv_empty = bar_kv_full + 8 * NS;
   const uint32_t bar_s = bar_kv_empty + 8 * NS;   // [2] S_t ready
   const uint32_t bar_p = bar_s + 16;              // [2] P_t written (128 arrivals)
   const uint32_t bar_o = bar_p + 16;              // [2] PV_t(j) complete
-  const uint32_t tmem_slot = bar_o + 16;
-  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+  const uint32_t bar_w_full = bar_o + 16;         // [2] mailbox slot published
+  const uint32_t bar_w_empty = bar_w_full + 16;   // [2] mailbox slot read by MMA thread + 8 softmax warps
+  const uint32_t tmem_slot = bar_w_empty + 16;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_al + Cfg::OFF_BAR + Cfg::NUM_BARS * 8);
+  uint8_t* mbox = smem_al + Cfg::OFF_MBOX;        // [2][32 B]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int head = blockIdx.x, bidb = blockIdx.z;
-  [[maybe_unused]] const bool trace_cta = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (threadIdx.x & 127) == 0 || (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && warp == TC5_MMA_WARP);
-  const int m_block = p.is_causal ? (gridDim.y - 1 - blockIdx.y) : blockIdx.y;   // heavy tiles first
-  const int kvh = head / p.group;
-  const SeqInfo si(p, bidb);
-  const int sq = si.sq, sk = si.sk;
-  const int m0 = m_block * 2 * TC5_BM;
-  if (m0 >= sq || sq * p.group < p.min_rows || sq * p.group > p.max_rows) return;
-  const int q_row0 = p.cu_seqlens_q ? p.cu_seqlens_q[bidb] : 0;     // row coordinate bases (varlen)
-  const int k_row0 = p.cu_seqlens_k ? p.cu_seqlens_k[bidb] : 0;
-  const int bcoord = p.cu_seqlens_q ? 0 : bidb;
-
-  const TileRange tr0 = tc5_range(p, m0, sq, sk), tr1 = tc5_range(p, m0 + TC5_BM, sq, sk);
-  const bool act0 = tr0.je > tr0.jb, act1 = tr1.je > tr1.jb;
-  const int j_begin = act0 ? (act1 ? min(tr0.jb, tr1.jb) : tr0.jb) : tr1.jb;
-  const int j_end = act0 || act1 ? max(tr0.je, tr1.je) : j_begin;
+  [[maybe_unused]] const bool trace_cta = blockIdx.x == 0 && ((threadIdx.x & 127) == 0 || warp == TC5_MMA_WARP);
 
   // ---- one-time setup ----
   if (warp == TC5_PRODUCER_WARP && lane == 0) {
     prefetch_tmap(&maps.q); prefetch_tmap(&maps.k); prefetch_tmap(&maps.v);
-    mbar_init(bar_q, 1); mbar_init(bar_q + 8, 1);
+    for (int t = 0; t < 2; t++) {
+      mbar_init(bar_q + 8 * t, 1); mbar_init(bar_q_empty + 8 * t, 1);
+      mbar_init(bar_s + 8 * t, 1); mbar_init(bar_p + 8 * t, 128); mbar_init(bar_o + 8 * t, 1);
+      mbar_init(bar_w_full + 8 * t, 1); mbar_init(bar_w_empty + 8 * t, 9);
+    }
     for (int i = 0; i < NS; i++) { mbar_init(bar_kv_full + 8 * i, 1); mbar_init(bar_kv_empty + 8 * i, 1); }
-    for (int t = 0; t < 2; t++) { mbar_init(bar_s + 8 * t, 1); mbar_init(bar_p + 8 * t, 128); mbar_init(bar_o + 8 * t, 1); }
     fence_barrier_init();
   }
   if (warp == TC5_MMA_WARP) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
@@ -166,83 +174,127 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
   // allocates each role against its own budget): the softmax threads hold a full 128-column S row
   if (warp == TC5_PRODUCER_WARP) {
     setmaxnreg_dec<TC5_REGS_OTHER>();
-    // =============================== TMA producer ===============================
-    if (elect_one()) {
-      for (int t = 0; t < 2; t++) {
-        if (!(t == 0 ? act0 : act1)) continue;
-        mbar_expect_tx(bar_q + 8 * t, Cfg::TILE_BYTES);
-        for (int c = 0; c < ND; c++)
-          tma_load_4d(q_sm + t * Cfg::TILE_BYTES + c * Cfg::SUB_BYTES, &maps.q, bar_q + 8 * t,
-                      c * 64, head, q_row0 + m0 + t * TC5_BM, bcoord);
+    // =============================== scheduler + TMA producer ===============================
+    // Work order: p.work_items (built by tc5_schedule_kernel, most expensive first) drawn through a
+    // global counter — longest-processing-time-first list scheduling over the persistent CTAs — or,
+    // for launches too small to need it, a static decode of (m_block, batch, head).
+    const int n_mb = (p.seqlen_q + 2 * TC5_BM - 1) / (2 * TC5_BM);
+    const int total = p.work_items ? p.work_header[1] * p.h : n_mb * p.b * p.h;
+    const int page = PAGED ? p.page_block_size : TC5_BN;
+    const int box_rows = min(page, TC5_BN), nbox = TC5_BN / box_rows;
+    int ring = 0;                 // K/V ring cursor, runs on across work units
+    int published = 0;
+    for (int wi = 0;; wi++) {
+      int w = 0;
+      if (p.work_items) { if (lane == 0) w = atomicAdd(p.work_header, 1); w = __shfl_sync(0xffffffffu, w, 0); }
+      else w = wi * gridDim.x + ((wi & 1) ? gridDim.x - 1 - blockIdx.x : blockIdx.x);   // boustrophedon
+      Tc5Work wk;
+      wk.valid = w < total;
+      if (wk.valid) {
+        const int unit = w / p.h;
+        wk.head = w - unit * p.h;
+        if (p.work_items) { const int2 it = p.work_items[unit]; wk.bidb = it.x; wk.m_block = it.y; }
+        else { wk.bidb = unit % p.b; const int mb = unit / p.b; wk.m_block = p.is_causal ? n_mb - 1 - mb : mb; }
+        const SeqInfo si(p, wk.bidb);
+        wk.sq = si.sq; wk.sk = si.sk;
+        wk.q_row0 = p.cu_seqlens_q ? p.cu_seqlens_q[wk.bidb] : 0;
+        wk.k_row0 = (!PAGED && p.cu_seqlens_k) ? p.cu_seqlens_k[wk.bidb] : 0;
+        const int rows = wk.sq * p.group;
+        if (wk.m_block * 2 * TC5_BM >= wk.sq || rows < p.min_rows || rows > p.max_rows) continue;   // static mode only
       }
+      const int ms = published & 1;
+      if (lane == 0) {
+        mbar_wait(bar_w_empty + 8 * ms, ((published >> 1) & 1) ^ 1);
+        *reinterpret_cast<int4*>(mbox + 32 * ms) = make_int4(wk.valid, wk.head, wk.bidb, wk.m_block);
+        *reinterpret_cast<int4*>(mbox + 32 * ms + 16) = make_int4(wk.sq, wk.sk, wk.q_row0, wk.k_row0);
+        mbar_arrive(bar_w_full + 8 * ms);
+      }
+      published++;
+      if (!wk.valid) break;
+
+      const int m0 = wk.m_block * 2 * TC5_BM, sq = wk.sq, sk = wk.sk;
+      const int kvh = wk.head / p.group;
+      const TileRange tr0 = tc5_range(p, m0, sq, sk), tr1 = tc5_range(p, m0 + TC5_BM, sq, sk);
+      const bool act0 = tr0.je > tr0.jb, act1 = tr1.je > tr1.jb;
+      const int j_begin = act0 ? (act1 ? min(tr0.jb, tr1.jb) : tr0.jb) : tr1.jb;
+      const int j_end = act0 || act1 ? max(tr0.je, tr1.je) : j_begin;
+      if (lane == 0) {
+        for (int t = 0; t < 2; t++) {
+          // both Q barriers flip once per work unit (inactive tile: plain arrive), so their parity is the unit's
+          mbar_wait(bar_q_empty + 8 * t, (published & 1));      // the previous unit's last QK_t has read Q_t
+          if (!(t == 0 ? act0 : act1)) { mbar_arrive(bar_q + 8 * t); continue; }
+          mbar_expect_tx(bar_q + 8 * t, Cfg::TILE_BYTES);
+          for (int c = 0; c < ND; c++)
+            tma_load_4d(q_sm + t * Cfg::TILE_BYTES + c * Cfg::SUB_BYTES, &maps.q, bar_q + 8 * t,
+                        c * 64, wk.head, wk.q_row0 + m0 + t * TC5_BM, p.cu_seqlens_q ? 0 : wk.bidb);
+        }
+      }
+      __syncwarp();
       if constexpr (!PAGED) {
-        int item = 0;
+        if (lane == 0) {
+          for (int j = j_begin; j < j_end; j++) {
+            for (int kv = 0; kv < 2; kv++, ring++) {
+              const int slot = ring % NS, round = ring / NS;
+              mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
+              mbar_expect_tx(bar_kv_full + 8 * slot, Cfg::TILE_BYTES);
+              for (int c = 0; c < ND; c++)
+                tma_load_4d(kv_sm + slot * Cfg::TILE_BYTES + c * Cfg::SUB_BYTES, kv == 0 ? &maps.k : &maps.v,
+                            bar_kv_full + 8 * slot, c * 64, kvh, wk.k_row0 + j * TC5_BN, p.cu_seqlens_k ? 0 : wk.bidb);
+            }
+          }
+        }
+        ring = __shfl_sync(0xffffffffu, ring, 0);
+      } else {
+        // Paged K/V (reference src/utils.h:297-315, kernel_traits.h:136-144): a 128-key tile is
+        // 128/box pages (or a slice of one big page); lane L looks up the block id of box L in the
+        // block table and issues that box's TMA loads itself, so the table indirection costs one
+        // coalesced load per tile.  The tensor maps are (d, heads, page_row, block).  The V tile that
+        // contains the end of the sequence is special: rows >= seqlen_k hold whatever the pool holds
+        // (possibly NaN) and 0 * NaN would poison P.V, so its boxes that reach past the end are copied
+        // by hand (valid rows) / zero-filled (the rest) in the 128-B swizzle TMA would have used.
+        const int* table = p.block_table + (int64_t)wk.bidb * p.block_table_batch_stride;
         for (int j = j_begin; j < j_end; j++) {
-          for (int kv = 0; kv < 2; kv++, item++) {
-            const int slot = item % NS, round = item / NS;
-            mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
-            mbar_expect_tx(bar_kv_full + 8 * slot, Cfg::TILE_BYTES);
-            for (int c = 0; c < ND; c++)
-              tma_load_4d(kv_sm + slot * Cfg::TILE_BYTES + c * Cfg::SUB_BYTES, kv == 0 ? &maps.k : &maps.v,
-                          bar_kv_full + 8 * slot, c * 64, kvh, k_row0 + j * TC5_BN, p.cu_seqlens_k ? 0 : bidb);
+          const int row0 = j * TC5_BN;
+          const int valid = min(TC5_BN, sk - row0);                    // rows of this tile inside the sequence (>= 1)
+          for (int kv = 0; kv < 2; kv++, ring++) {
+            const int slot = ring % NS, round = ring / NS;
+            if (lane == 0) mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
+            __syncwarp();
+            const uint32_t dst = kv_sm + slot * Cfg::TILE_BYTES, bar = bar_kv_full + 8 * slot;
+            const bool tail = kv == 1 && valid < TC5_BN;
+            const int n_tma_boxes = tail ? valid / box_rows : nbox;      // boxes entirely inside the sequence
+            if (tail) {
+              const T* vbase = reinterpret_cast<const T*>(p.v) + (int64_t)kvh * p.v_head_stride;
+              const int r_begin = n_tma_boxes * box_rows;
+              for (int idx = lane; idx < (TC5_BN - r_begin) * ND * 8; idx += 32) {
+                const int ch = idx & 7, c = (idx >> 3) % ND, r = r_begin + (idx >> 3) / ND;
+                uint4 val = make_uint4(0, 0, 0, 0);
+                if (r < valid) {
+                  const int g = row0 + r, pg = g / page;
+                  const int blk = table[min(pg, p.max_blocks_per_seq - 1)];
+                  val = *reinterpret_cast<const uint4*>(vbase + (int64_t)blk * p.v_batch_stride +
+                                                        (int64_t)(g - pg * page) * p.v_row_stride + c * 64 + ch * 8);
+                }
+                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + c * Cfg::SUB_BYTES + r * 128 + ((ch ^ (r & 7)) << 4)),
+                             "r"(val.x), "r"(val.y), "r"(val.z), "r"(val.w) : "memory");
+              }
+              fence_proxy_async_smem();
+            }
+            __syncwarp();
+            if (lane == 0) mbar_expect_tx(bar, (uint32_t)(n_tma_boxes * box_rows * 128 * ND));
+            __syncwarp();
+            if (lane < n_tma_boxes) {
+              const int g = row0 + lane * box_rows, pg = g / page;
+              const int blk = table[min(pg, p.max_blocks_per_seq - 1)];
+              for (int c = 0; c < ND; c++)
+                tma_load_4d(dst + c * Cfg::SUB_BYTES + lane * box_rows * 128, kv == 0 ? &maps.k : &maps.v, bar,
+                            c * 64, kvh, g - pg * page, blk);
+            }
           }
         }
       }
     }
     __syncwarp();
-    if constexpr (PAGED) {
-      // Paged K/V (reference src/utils.h:297-315, kernel_traits.h:136-144): a 128-key tile is
-      // 128/box pages (or a slice of one big page); lane L looks up the block id of box L in the
-      // block table and issues that box's TMA loads itself, so the table indirection costs one
-      // coalesced load per tile.  The tensor maps are (d, heads, page_row, block).  The V tile that
-      // contains the end of the sequence is special: rows >= seqlen_k hold whatever the pool holds
-      // (possibly NaN) and 0 * NaN would poison P.V, so its boxes that reach past the end are copied
-      // by hand (valid rows) / zero-filled (the rest) in the 128-B swizzle TMA would have used.
-      const int page = p.page_block_size;
-      const int box_rows = min(page, TC5_BN), nbox = TC5_BN / box_rows;
-      const int* table = p.block_table + (int64_t)bidb * p.block_table_batch_stride;
-      int item = 0;
-      for (int j = j_begin; j < j_end; j++) {
-        const int row0 = j * TC5_BN;
-        const int valid = min(TC5_BN, sk - row0);                    // rows of this tile inside the sequence (>= 1)
-        for (int kv = 0; kv < 2; kv++, item++) {
-          const int slot = item % NS, round = item / NS;
-          if (lane == 0) mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
-          __syncwarp();
-          const uint32_t dst = kv_sm + slot * Cfg::TILE_BYTES, bar = bar_kv_full + 8 * slot;
-          const bool tail = kv == 1 && valid < TC5_BN;
-          const int n_tma_boxes = tail ? valid / box_rows : nbox;      // boxes entirely inside the sequence
-          if (tail) {
-            const T* vbase = reinterpret_cast<const T*>(p.v) + (int64_t)kvh * p.v_head_stride;
-            const int r_begin = n_tma_boxes * box_rows;
-            for (int idx = lane; idx < (TC5_BN - r_begin) * ND * 8; idx += 32) {
-              const int ch = idx & 7, c = (idx >> 3) % ND, r = r_begin + (idx >> 3) / ND;
-              uint4 val = make_uint4(0, 0, 0, 0);
-              if (r < valid) {
-                const int g = row0 + r, pg = g / page;
-                const int blk = table[min(pg, p.max_blocks_per_seq - 1)];
-                val = *reinterpret_cast<const uint4*>(vbase + (int64_t)blk * p.v_batch_stride +
-                                                      (int64_t)(g - pg * page) * p.v_row_stride + c * 64 + ch * 8);
-              }
-              asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + c * Cfg::SUB_BYTES + r * 128 + ((ch ^ (r & 7)) << 4)),
-                           "r"(val.x), "r"(val.y), "r"(val.z), "r"(val.w) : "memory");
-            }
-            fence_proxy_async_smem();
-          }
-          __syncwarp();
-          if (lane == 0) mbar_expect_tx(bar, (uint32_t)(n_tma_boxes * box_rows * 128 * ND));
-          __syncwarp();
-          if (lane < n_tma_boxes) {
-            const int g = row0 + lane * box_rows, pg = g / page;
-            const int blk = table[min(pg, p.max_blocks_per_seq - 1)];
-            for (int c = 0; c < ND; c++)
-              tma_load_4d(dst + c * Cfg::SUB_BYTES + lane * box_rows * 128, kv == 0 ? &maps.k : &maps.v, bar,
-                          c * 64, kvh, g - pg * page, blk);
-          }
-        }
-      }
-      __syncwarp();
-    }
   } else if (warp == TC5_MMA_WARP) {
     setmaxnreg_dec<TC5_REGS_OTHER>();
     // =============================== MMA issuer ===============================
@@ -250,67 +302,98 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
     // in-order stream is what keeps the two softmax warpgroups in ANTI-phase (one exponentiates
     // while the other tile's MMAs run); two independent issuers drift into phase and halve the
     // MUFU rate each warpgroup sees.  Only one barrier wait (P_t) sits on a tile's chain: the
-    // arrival of V_j and K_{j+1} is checked before it.
+    // arrival of V_j and K_{j+1} is checked before it.  Work units follow one another without
+    // draining: the first QK of the next unit is issued right behind the last PV of this one, so
+    // S is ready when a softmax warpgroup returns from its epilogue.
     constexpr uint32_t idesc_qk = make_idesc(IS_BF16, TC5_BM, TC5_BN, false);
     constexpr uint32_t idesc_pv = make_idesc(IS_BF16, TC5_BM, D, true);
+    // descriptor = constant high part | (smem address >> 4); the k-step loops are NOT unrolled: one MMA
+    // occupies the tensor pipe for 64 clk, so a few scalar instructions per issue are free, and the
+    // issuer's 56 registers hold no precomputed descriptor tables (spills would sit on the P -> PV chain)
+    constexpr uint64_t DESC_KMAJOR = ((uint64_t)(16 >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+    constexpr uint64_t DESC_V = ((uint64_t)(Cfg::SUB_BYTES >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
     if (elect_one()) {
-      auto active = [&](int t, int j) { return t == 0 ? (j >= tr0.jb && j < tr0.je) : (j >= tr1.jb && j < tr1.je); };
-      // S_t = Q_t K_j^T : A = Q (K-major, SW128), B = K (K-major, SW128); D/16 k-steps
-      auto issue_qk = [&](int t, int j, int slot, bool release) {
-        const uint32_t qa = q_sm + t * Cfg::TILE_BYTES, kb = kv_sm + slot * Cfg::TILE_BYTES;
+      int ring = 0;               // K/V ring cursor (same sequence of items as the producer's)
+      int pbits = 0;              // bit t: parity of the softmax iterations of tile t so far (phase of bar_p)
+      [[maybe_unused]] int trace_it = 0;
+      for (int wi = 0;; wi++) {
+        const int ms = wi & 1;
+        mbar_wait(bar_w_full + 8 * ms, (wi >> 1) & 1);
+        Tc5Work wk;
+        tc5_read_work(mbox + 32 * ms, wk);
+        mbar_arrive(bar_w_empty + 8 * ms);
+        if (!wk.valid) break;
+        const int m0 = wk.m_block * 2 * TC5_BM;
+        const TileRange tr0 = tc5_range(p, m0, wk.sq, wk.sk), tr1 = tc5_range(p, m0 + TC5_BM, wk.sq, wk.sk);
+        const bool act0 = tr0.je > tr0.jb, act1 = tr1.je > tr1.jb;
+        const int j_begin = act0 ? (act1 ? min(tr0.jb, tr1.jb) : tr0.jb) : tr1.jb;
+        const int j_end = act0 || act1 ? max(tr0.je, tr1.je) : j_begin;
+        auto active = [&](int t, int j) { return t == 0 ? (j >= tr0.jb && j < tr0.je) : (j >= tr1.jb && j < tr1.je); };
+        // S_t = Q_t K_j^T : A = Q (K-major, SW128), B = K (K-major, SW128); D/16 k-steps
+        auto issue_qk = [&](int t, int j, int slot, bool release) {
+          const uint32_t qa = ((q_sm + t * Cfg::TILE_BYTES) & 0x3FFFF) >> 4, kb = ((kv_sm + slot * Cfg::TILE_BYTES) & 0x3FFFF) >> 4;
 #pragma unroll
-        for (int ks = 0; ks < D / 16; ks++) {
-          const uint32_t off = (ks / 4) * Cfg::SUB_BYTES + (ks % 4) * 32;
-          umma_ss(tmem + Cfg::TM_S + t * 128, make_desc_sw128(qa + off, 16, 1024),
-                  make_desc_sw128(kb + off, 16, 1024), idesc_qk, ks > 0);
-        }
-        TC5_TRACE(2, j - 1 - j_begin, t * 8 + 5);
-        umma_commit(bar_s + 8 * t);
-        if (release) umma_commit(bar_kv_empty + 8 * slot);
-      };
-      if (act0) mbar_wait(bar_q, 0);
-      if (act1) mbar_wait(bar_q + 8, 0);
-      if (j_begin < j_end) {
-        mbar_wait(bar_kv_full, 0);            // item 0 = K_{j_begin}: slot 0, first round
-        tc_fence_after();
-        const bool a0 = active(0, j_begin), a1 = active(1, j_begin);
-        if (a0) issue_qk(0, j_begin, 0, !a1);
-        if (a1) issue_qk(1, j_begin, 0, true);
-      }
-      for (int j = j_begin; j < j_end; j++) {
-        const int vi = 2 * (j - j_begin) + 1, ki = vi + 1;
-        const int vslot = vi % NS, kslot = ki % NS;
-        const bool more = j + 1 < j_end;
-        TC5_TRACE(2, j - j_begin, 0);
-        mbar_wait(bar_kv_full + 8 * vslot, (vi / NS) & 1);
-        if (more) mbar_wait(bar_kv_full + 8 * kslot, (ki / NS) & 1);
-        TC5_TRACE(2, j - j_begin, 1);
-        const bool a0 = active(0, j), a1 = active(1, j);
-        const bool k0 = more && active(0, j + 1), k1 = more && active(1, j + 1);
-#pragma unroll
-        for (int t = 0; t < 2; t++) {
-          const bool a = t == 0 ? a0 : a1, kq = t == 0 ? k0 : k1;
-          const int jb_t = t == 0 ? tr0.jb : tr1.jb;
-          if (a) {
-            // O_t (+)= P_t V_j : A = P (TMEM), B = V (MN-major, SW128); 8 k-steps of 16 keys
-            mbar_wait(bar_p + 8 * t, (uint32_t)((j - jb_t) & 1));
-            TC5_TRACE(2, j - j_begin, t * 8 + 2);
-            tc_fence_after();
-            const uint32_t vb = kv_sm + vslot * Cfg::TILE_BYTES;
-#pragma unroll
-            for (int kk = 0; kk < TC5_BN / 16; kk++)
-              umma_ts(tmem + Cfg::TM_O + t * 128, tmem + Cfg::TM_S + t * 128 + kk * 8,
-                      make_desc_sw128(vb + kk * 2048, Cfg::SUB_BYTES, 1024), idesc_pv, (j > jb_t) || kk > 0);
-            TC5_TRACE(2, j - j_begin, t * 8 + 3);
-            umma_commit(bar_o + 8 * t);
-            if (t == 1 || !a1) umma_commit(bar_kv_empty + 8 * vslot);
-            TC5_TRACE(2, j - j_begin, t * 8 + 4);
+          for (int ks = 0; ks < D / 16; ks++) {
+            const uint32_t off = (ks >> 2) * (Cfg::SUB_BYTES >> 4) + (ks & 3) * 2;
+            umma_ss(tmem + Cfg::TM_S + t * 128, DESC_KMAJOR | (qa + off), DESC_KMAJOR | (kb + off), idesc_qk, ks > 0);
           }
-          if (kq) issue_qk(t, j + 1, kslot, t == 1 || !k1);
-          TC5_TRACE(2, j - j_begin, t * 8 + 6);
+          TC5_TRACE(2, trace_it + j - 1 - j_begin, t * 8 + 5);
+          umma_commit(bar_s + 8 * t);
+          if (release) umma_commit(bar_kv_empty + 8 * slot);
+          if (j + 1 == (t == 0 ? tr0.je : tr1.je)) umma_commit(bar_q_empty + 8 * t);   // Q_t may be overwritten
+        };
+        mbar_wait(bar_q, wi & 1);
+        mbar_wait(bar_q + 8, wi & 1);
+        if (!act0) mbar_arrive(bar_q_empty);
+        if (!act1) mbar_arrive(bar_q_empty + 8);
+        if (j_begin < j_end) {
+          const int slot = ring % NS;
+          mbar_wait(bar_kv_full + 8 * slot, (ring / NS) & 1);            // K_{j_begin}
+          tc_fence_after();
+          const bool a0 = active(0, j_begin), a1 = active(1, j_begin);
+          if (a0) issue_qk(0, j_begin, slot, !a1);
+          if (a1) issue_qk(1, j_begin, slot, true);
         }
-        if (!a0 && !a1) umma_commit(bar_kv_empty + 8 * vslot);          // unreachable for monotone windows
-        if (more && !k0 && !k1) umma_commit(bar_kv_empty + 8 * kslot);
+        for (int j = j_begin; j < j_end; j++) {
+          const int vi = ring + 2 * (j - j_begin) + 1, ki = vi + 1;
+          const int vslot = vi % NS, kslot = ki % NS;
+          const bool more = j + 1 < j_end;
+          TC5_TRACE(2, trace_it + j - j_begin, 0);
+          mbar_wait(bar_kv_full + 8 * vslot, (vi / NS) & 1);
+          if (more) mbar_wait(bar_kv_full + 8 * kslot, (ki / NS) & 1);
+          TC5_TRACE(2, trace_it + j - j_begin, 1);
+          const bool a0 = active(0, j), a1 = active(1, j);
+          const bool k0 = more && active(0, j + 1), k1 = more && active(1, j + 1);
+#pragma unroll 1
+          for (int t = 0; t < 2; t++) {
+            const bool a = t == 0 ? a0 : a1, kq = t == 0 ? k0 : k1;
+            const int jb_t = t == 0 ? tr0.jb : tr1.jb;
+            if (a) {
+              // O_t (+)= P_t V_j : A = P (TMEM), B = V (MN-major, SW128); 8 k-steps of 16 keys
+              mbar_wait(bar_p + 8 * t, (uint32_t)(((pbits >> t) ^ (j - jb_t)) & 1));
+              TC5_TRACE(2, trace_it + j - j_begin, t * 8 + 2);
+              tc_fence_after();
+              const uint32_t vb = ((kv_sm + vslot * Cfg::TILE_BYTES) & 0x3FFFF) >> 4;
+#pragma unroll
+              for (int kk = 0; kk < TC5_BN / 16; kk++)
+                umma_ts(tmem + Cfg::TM_O + t * 128, tmem + Cfg::TM_S + t * 128 + kk * 8,
+                        DESC_V | (vb + kk * (2048 >> 4)), idesc_pv, (j > jb_t) || kk > 0);
+              TC5_TRACE(2, trace_it + j - j_begin, t * 8 + 3);
+              umma_commit(bar_o + 8 * t);
+              if (t == 1 || !a1) umma_commit(bar_kv_empty + 8 * vslot);
+              TC5_TRACE(2, trace_it + j - j_begin, t * 8 + 4);
+            }
+            if (kq) issue_qk(t, j + 1, kslot, t == 1 || !k1);
+            TC5_TRACE(2, trace_it + j - j_begin, t * 8 + 6);
+          }
+          if (!a0 && !a1) umma_commit(bar_kv_empty + 8 * vslot);          // unreachable for monotone windows
+          if (more && !k0 && !k1) umma_commit(bar_kv_empty + 8 * kslot);
+        }
+        ring += 2 * (j_end - j_begin);
+        pbits ^= ((tr0.je - tr0.jb) & 1) | (((tr1.je - tr1.jb) & 1) << 1);
+#ifdef FA_TC5_TRACE
+        trace_it += j_end - j_begin;
+#endif
       }
     }
     __syncwarp();
@@ -325,6 +408,60 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
   tc_fence_before();
   __syncthreads();
   if (warp == TC5_MMA_WARP) { tc_fence_after(); tmem_dealloc(tmem, 512); }
+}
+
+// Builds the work list of the persistent kernel: one (sequence, m_block) entry per 256 query rows
+// that pass the row filter, ordered by decreasing number of KV tiles (counting sort), and resets
+// the draw counter.  header = {counter, n_units}.  One CTA; runs right before the attention kernel.
+constexpr int TC5_SCHED_THREADS = 1024, TC5_SCHED_BINS = 2048;
+__global__ void __launch_bounds__(TC5_SCHED_THREADS)
+tc5_schedule_kernel(const __grid_constant__ KParams p, int2* items, int* header, int max_items) {
+  __shared__ int bins[TC5_SCHED_BINS];       // histogram by cost, then running offsets
+  __shared__ int warp_sums[32];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < TC5_SCHED_BINS; i += TC5_SCHED_THREADS) bins[i] = 0;
+  __syncthreads();
+  auto cost_of = [&](int mb, int sq, int sk) {
+    const TileRange a = tc5_range(p, mb * 2 * TC5_BM, sq, sk), b = tc5_range(p, mb * 2 * TC5_BM + TC5_BM, sq, sk);
+    return min((a.je - a.jb) + (b.je - b.jb), TC5_SCHED_BINS - 1);
+  };
+  auto live = [&](int sq) { const int rows = sq * p.group; return sq > 0 && rows >= p.min_rows && rows <= p.max_rows; };
+  for (int s = tid; s < p.b; s += TC5_SCHED_THREADS) {
+    const SeqInfo si(p, s);
+    if (!live(si.sq)) continue;
+    const int n = (si.sq + 2 * TC5_BM - 1) / (2 * TC5_BM);
+    for (int mb = 0; mb < n; mb++) atomicAdd(&bins[TC5_SCHED_BINS - 1 - cost_of(mb, si.sq, si.sk)], 1);   // bin 0 = most expensive
+  }
+  __syncthreads();
+  // exclusive prefix sum over the 2048 bins (2 per thread)
+  const int a = bins[2 * tid], b = bins[2 * tid + 1];
+  int v = a + b;
+  const int lane = tid & 31, wp = tid >> 5;
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += y; }
+  if (lane == 31) warp_sums[wp] = incl;
+  __syncthreads();
+  if (wp == 0) {
+    int s = warp_sums[lane], si = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, si, o); if (lane >= o) si += y; }
+    warp_sums[lane] = si - s;
+  }
+  __syncthreads();
+  const int excl = warp_sums[wp] + incl - v;
+  bins[2 * tid] = excl; bins[2 * tid + 1] = excl + a;
+  if (tid == TC5_SCHED_THREADS - 1) { header[0] = 0; header[1] = min(excl + v, max_items); }
+  __syncthreads();
+  for (int s = tid; s < p.b; s += TC5_SCHED_THREADS) {
+    const SeqInfo si(p, s);
+    if (!live(si.sq)) continue;
+    const int n = (si.sq + 2 * TC5_BM - 1) / (2 * TC5_BM);
+    for (int mb = 0; mb < n; mb++) {
+      const int pos = atomicAdd(&bins[TC5_SCHED_BINS - 1 - cost_of(mb, si.sq, si.sk)], 1);
+      if (pos < max_items) items[pos] = make_int2(s, mb);
+    }
+  }
 }
 
 // =========================================================================================
@@ -385,32 +522,43 @@ bool tc5_supported(const KParams& p) {
 }
 
 template <typename T, int D, bool HAS_ALIBI, bool PAGED>
-static cudaError_t launch_tc5_t(const KParams& p, const Tc5Maps& maps, cudaStream_t stream) {
+static cudaError_t launch_tc5_t(const KParams& p, const Tc5Maps& maps, int grid, cudaStream_t stream) {
   using Cfg = Tc5Cfg<D>;
   auto kern = fa_prefill_tc5_kernel<T, D, HAS_ALIBI, PAGED>;
   FA_SET_SMEM_ONCE(kern, Cfg::SMEM);
-  dim3 grid(p.h, (p.seqlen_q + 2 * TC5_BM - 1) / (2 * TC5_BM), p.b);
   kern<<<grid, TC5_THREADS, Cfg::SMEM, stream>>>(p, maps);
   return cudaGetLastError();
 }
 
 template <typename T, int D>
-static cudaError_t launch_tc5_d(const KParams& p, const Tc5Maps& maps, cudaStream_t stream) {
+static cudaError_t launch_tc5_d(const KParams& p, const Tc5Maps& maps, int grid, cudaStream_t stream) {
   const bool alibi = p.alibi_slopes != nullptr;
-  if (p.block_table) return alibi ? launch_tc5_t<T, D, true, true>(p, maps, stream) : launch_tc5_t<T, D, false, true>(p, maps, stream);
-  return alibi ? launch_tc5_t<T, D, true, false>(p, maps, stream) : launch_tc5_t<T, D, false, false>(p, maps, stream);
+  if (p.block_table) return alibi ? launch_tc5_t<T, D, true, true>(p, maps, grid, stream) : launch_tc5_t<T, D, false, true>(p, maps, grid, stream);
+  return alibi ? launch_tc5_t<T, D, true, false>(p, maps, grid, stream) : launch_tc5_t<T, D, false, false>(p, maps, grid, stream);
+}
+
+// Upper bound on the number of (sequence, m_block) work units, from host-side shapes only.
+int64_t tc5_max_units(const KParams& p, int64_t total_q) {
+  const int64_t per = 2 * TC5_BM;
+  return p.cu_seqlens_q ? total_q / per + p.b : (int64_t)p.b * ((p.seqlen_q + per - 1) / per);
+}
+// Workspace for the cost-sorted work list; 0 when the launch is small enough for the static order.
+size_t tc5_workspace_bytes(const KParams& p, int64_t total_q, int num_sms) {
+  const int64_t units = tc5_max_units(p, total_q);
+  if (units * p.h <= num_sms) return 0;
+  return 16 + (size_t)units * sizeof(int2);
 }
 
 #ifdef FA_TC5_TRACE
 // Debug only: a device buffer for the timeline, dumped to $FA_B200_TRACE_FILE after each launch.
-static cudaError_t launch_prefill_tc5_impl(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, cudaStream_t stream);
-cudaError_t launch_prefill_tc5(const KParams& p_in, bool is_bf16, int64_t total_q, int64_t total_k, cudaStream_t stream) {
+static cudaError_t launch_prefill_tc5_impl(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, int num_sms, cudaStream_t stream);
+cudaError_t launch_prefill_tc5(const KParams& p_in, bool is_bf16, int64_t total_q, int64_t total_k, int num_sms, cudaStream_t stream) {
   static long long* buf = nullptr;
   const size_t n = 3 * 128 * 16;
   if (!buf) cudaMalloc(&buf, n * sizeof(long long));
   cudaMemsetAsync(buf, 0, n * sizeof(long long), stream);
   KParams p = p_in; p.trace = buf;
-  cudaError_t e = launch_prefill_tc5_impl(p, is_bf16, total_q, total_k, stream);
+  cudaError_t e = launch_prefill_tc5_impl(p, is_bf16, total_q, total_k, num_sms, stream);
   const char* path = getenv("FA_B200_TRACE_FILE");
   if (e == cudaSuccess && path) {
     std::vector<long long> h(n);
@@ -420,9 +568,9 @@ cudaError_t launch_prefill_tc5(const KParams& p_in, bool is_bf16, int64_t total_
   }
   return e;
 }
-static cudaError_t launch_prefill_tc5_impl(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, cudaStream_t stream) {
+static cudaError_t launch_prefill_tc5_impl(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, int num_sms, cudaStream_t stream) {
 #else
-cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, cudaStream_t stream) {
+cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, int num_sms, cudaStream_t stream) {
 #endif
   Tc5Maps maps;
   const bool varlen = p.cu_seqlens_q != nullptr;
@@ -439,8 +587,17 @@ cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, 
          make_map(&maps.v, p.v, is_bf16, TC5_BN, p.d, p.h_k, k_rows, kvarlen ? 1 : p.b, p.v_head_stride, p.v_row_stride, p.v_batch_stride);
   }
   if (!ok) return cudaErrorInvalidValue;
-  if (is_bf16) return p.d == 64 ? launch_tc5_d<__nv_bfloat16, 64>(p, maps, stream) : launch_tc5_d<__nv_bfloat16, 128>(p, maps, stream);
-  return p.d == 64 ? launch_tc5_d<__half, 64>(p, maps, stream) : launch_tc5_d<__half, 128>(p, maps, stream);
+  const int64_t units = tc5_max_units(p, total_q);
+  int grid = (int)std::min<int64_t>(units * p.h, num_sms);
+  if (grid <= 0) return cudaSuccess;
+  if (p.work_items) {
+    tc5_schedule_kernel<<<1, TC5_SCHED_THREADS, 0, stream>>>(p, p.work_items, p.work_header, (int)units);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    grid = num_sms;
+  }
+  if (is_bf16) return p.d == 64 ? launch_tc5_d<__nv_bfloat16, 64>(p, maps, grid, stream) : launch_tc5_d<__nv_bfloat16, 128>(p, maps, grid, stream);
+  return p.d == 64 ? launch_tc5_d<__half, 64>(p, maps, grid, stream) : launch_tc5_d<__half, 128>(p, maps, grid, stream);
 }
 
 }  // namespace fa
