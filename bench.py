@@ -40,14 +40,29 @@ def prefill_flops(seqlens=SEQLENS_C2, h=H, d=D):
 
 
 class ClockSampler:
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock + throttle reasons sampled DURING the timed region (B200_PROFILING.md clocks line): NVML polled
+    every 2 ms from a thread; falls back to `nvidia-smi -lms 100` when pynvml is unavailable."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index=0):
-        self.index, self.samples, self.proc = index, [], None
+        self.index, self.samples, self.proc, self.nv, self.stop_flag = index, [], None, None, False
+        self.sm, self.mx, self.reasons = [], None, set()
 
     def start(self):
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[self.index]) if vis and vis.split(",")[self.index].isdigit() else self.index
+            self.h = nv.nvmlDeviceGetHandleByIndex(idx)
+            self.mx = float(nv.nvmlDeviceGetMaxClockInfo(self.h, nv.NVML_CLOCK_SM))
+            self.nv = nv
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
+        except Exception:
+            self.nv = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "100"],
@@ -56,11 +71,33 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def _poll(self):
+        nv = self.nv
+        bits = {"hw_slowdown": nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8,
+                "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+        get_reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                r = int(get_reasons(self.h))
+                for n, b in bits.items():
+                    if r & b:
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.002)
+
     def _read(self):
         for line in self.proc.stdout:
             self.samples.append(line.strip())
 
     def stop(self):
+        if self.nv is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=1.0)
+            sm = sorted(self.sm)
+            return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_min_mhz": sm[0] if sm else None, "sm_max_mhz": self.mx,
+                    "reasons": sorted(self.reasons), "samples": len(sm), "source": "nvml 2 ms poll"}
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -80,7 +117,17 @@ class ClockSampler:
                     reasons.add(n)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "source": "nvidia-smi -lms 100"}
+
+
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` summary
+    (profiles/traffic.json, written by tools/ncu_summary.py); None when no capture is committed."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(kernel)
+    except Exception:
+        return None
 
 
 def make_prefill_inputs(dev, seed=0):
@@ -246,9 +293,9 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": (qh.numel() + kh.numel() + vh.numel()) * 2,
                     "d2h_bytes_per_step": out_h.numel() * 2, "ms_per_step": ms_e2e,
                     "note": "pinned host q,k,v -> device, attention, out -> pinned host every step; 3 streams, double-buffered"},
-            "gpu_launches": launches_per_step * (args.steps * 2 + 2),
+            "gpu_launches": launches_per_step * args.steps * 2,   # kernel-only region + e2e region
             "roofline": {"bound": "tensor", "achieved": per_gpu_tflops, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
-                         "frac": per_gpu_tflops / pk["bf16_tflops"], "traffic": None, "peak_source": pk_src + " burst (cuBLAS bf16)",
+                         "frac": per_gpu_tflops / pk["bf16_tflops"], "traffic": ncu_traffic("prefill_c2"), "peak_source": pk_src + " burst (cuBLAS bf16)",
                          "frac_of_sustained": per_gpu_tflops / pk["bf16_tflops_sustained"], "frac_of_nominal_2250": per_gpu_tflops / 2250.0,
                          "flops_per_launch": flops},
             "clocks": clocks}
@@ -299,7 +346,7 @@ def bench_decode(fa, ext, dev, pk, pk_src, args, b=256, ctx=4096, page=16):
                        "l2": "KV pool 5.4 GB >> L2"},
             "kernel_used": info.get("kernel_used"), "num_splits": info.get("num_splits"),
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
-                         "traffic": None, "peak_source": pk_src + " (copy)", "frac_of_nominal_8000": gbs / 8000.0,
+                         "traffic": ncu_traffic("decode_c3"), "peak_source": pk_src + " (copy)", "frac_of_nominal_8000": gbs / 8000.0,
                          "bytes_per_launch": nbytes}}
 
 

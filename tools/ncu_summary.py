@@ -1,8 +1,14 @@
 """Summarise an .ncu-rep (raw page) into the handful of metrics the roofline discussion needs.
-  python tools/ncu_summary.py gpurun_out/prof.ncu-rep [extra_regex]"""
-import csv, io, re, subprocess, sys
-rep = sys.argv[1]
-extra = sys.argv[2] if len(sys.argv) > 2 else None
+  python tools/ncu_summary.py gpurun_out/prof.ncu-rep [extra_regex] [--traffic KEY]
+--traffic KEY records dram read+write bytes of the first kernel in profiles/traffic.json under KEY
+(bench.py reports it as roofline.traffic)."""
+import csv, io, json, os, re, subprocess, sys
+argv = sys.argv[1:]
+traffic_key = None
+if "--traffic" in argv:
+    i = argv.index("--traffic"); traffic_key = argv[i + 1]; del argv[i:i + 2]
+rep = argv[0]
+extra = argv[1] if len(argv) > 1 else None
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units = rows[0], rows[1]
@@ -17,3 +23,16 @@ for r in rows[2:]:
     for h, u, v in zip(hdr, units, r):
         if pat.search(h):
             print(f"  {h} [{u}] = {v}")
+
+if traffic_key and len(rows) > 2:
+    r = rows[2]
+    def val(name):
+        i = hdr.index(name)
+        v, u = float(r[i].replace(",", "")), units[i].lower()
+        return v * {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}.get(u, 1)
+    tot = val("dram__bytes_read.sum") + val("dram__bytes_write.sum")
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "traffic.json")
+    d = json.load(open(path)) if os.path.exists(path) else {}
+    d[traffic_key] = tot
+    json.dump(d, open(path, "w"), indent=1)
+    print(f"traffic[{traffic_key}] = {tot:.4g} bytes per launch -> {path}")

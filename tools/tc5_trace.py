@@ -34,6 +34,9 @@ def main():
     for _ in range(3):
         fa.flash_attn_func(q, k, v, causal=a.causal)
     torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); fa.flash_attn_func(q, k, v, causal=a.causal); e1.record(); torch.cuda.synchronize()
+    print(f"one call (trace build, incl. trace memset + schedule kernel + sync): {e0.elapsed_time(e1) * 1e3:.1f} us")
     raw = open(TRACE, "rb").read()
     vals = struct.unpack(f"{len(raw) // 8}q", raw)
     ev = lambda role, it, e: vals[(role * 128 + it) * 16 + e]
@@ -51,6 +54,10 @@ def main():
         m = [ev(2, it, i) - t00 for i in range(16)]
         print(f"        MMA : top@{m[0]:7d} KV +{m[1]-m[0]:4d} | t0 P@{m[2]:7d} PVissue +{m[3]-m[2]:4d} commit +{m[4]-m[3]:4d} QKissue +{m[5]-m[4]:4d} commit +{m[6]-m[5]:4d}"
               f" | t1 P@{m[10]:7d} (waited {m[10]-m[6]:5d}) PVissue +{m[11]-m[10]:4d} commit +{m[12]-m[11]:4d} QKissue +{m[13]-m[12]:4d} commit +{m[14]-m[13]:4d}")
+    c0, n0, c1, n1, its = (ev(2, 127, i) for i in (12, 13, 14, 15, 11))
+    if n1 > n0:
+        print(f"CTA 0 lifetime: {c1 - c0} SM clk in {(n1 - n0) / 1e3:.1f} us -> {(c1 - c0) / (n1 - n0) * 1e3:.0f} MHz effective; "
+              f"{its} KV iterations -> {(c1 - c0) / max(its, 1):.0f} clk per iteration overall")
     # average period
     per = (ev(0, a.first + a.count, 5) - ev(0, a.first, 5)) / a.count
     print(f"average period per KV tile (WG0 P_hi to P_hi): {per:.0f} clk; tensor work per period = 2048 clk -> {2048 / per:.1%} of peak")

@@ -33,7 +33,7 @@ using namespace sm100;
 // Debug timeline (tools/tc5_trace.py): -DFA_TC5_TRACE builds record clock64 stamps of CTA (0,0,0):
 // trace[role][iteration][event], role 0/1 = softmax warpgroup 0/1 (its first thread), 2 = MMA issuer.
 #ifdef FA_TC5_TRACE
-#define TC5_TRACE(role, iter, ev) do { if (p.trace && trace_cta && (iter) < 128) p.trace[((role) * 128 + (iter)) * 16 + (ev)] = clock64(); } while (0)
+#define TC5_TRACE(role, iter, ev) do { if (p.trace && trace_cta && (iter) < 127) p.trace[((role) * 128 + (iter)) * 16 + (ev)] = clock64(); } while (0)
 #else
 #define TC5_TRACE(role, iter, ev) do { } while (0)
 #endif
@@ -316,12 +316,25 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
       int ring = 0;               // K/V ring cursor (same sequence of items as the producer's)
       int pbits = 0;              // bit t: parity of the softmax iterations of tile t so far (phase of bar_p)
       [[maybe_unused]] int trace_it = 0;
+#ifdef FA_TC5_TRACE
+      if (p.trace && trace_cta) {   // SM clock vs wall clock over this CTA's whole life: effective frequency
+        long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        p.trace[(2 * 128 + 127) * 16 + 12] = clock64(); p.trace[(2 * 128 + 127) * 16 + 13] = ns;
+      }
+#endif
       for (int wi = 0;; wi++) {
         const int ms = wi & 1;
         mbar_wait(bar_w_full + 8 * ms, (wi >> 1) & 1);
         Tc5Work wk;
         tc5_read_work(mbox + 32 * ms, wk);
         mbar_arrive(bar_w_empty + 8 * ms);
+#ifdef FA_TC5_TRACE
+        if (!wk.valid && p.trace && trace_cta) {
+          long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+          p.trace[(2 * 128 + 127) * 16 + 14] = clock64(); p.trace[(2 * 128 + 127) * 16 + 15] = ns;
+          p.trace[(2 * 128 + 127) * 16 + 11] = trace_it;
+        }
+#endif
         if (!wk.valid) break;
         const int m0 = wk.m_block * 2 * TC5_BM;
         const TileRange tr0 = tc5_range(p, m0, wk.sq, wk.sk), tr1 = tc5_range(p, m0 + TC5_BM, wk.sq, wk.sk);
