@@ -61,17 +61,56 @@ def _alibi(P, alibi_slopes, batch, heads, device):
     P.alibi_slopes_batch_stride = alibi_slopes.stride(0) if alibi_slopes.dim() == 2 else 0
 
 
+_ws_cache = {}             # (device index, stream handle) -> persistent workspace tensor
+
+
 def _run(P: FaFwdParams, op: int, fn, device) -> None:
+    """One library call.  The split-KV / work-list workspace is a persistent per-(device, stream)
+    buffer (calls on one stream are ordered, so they can share it), grown when the library says it is
+    too small; under CUDA-graph capture a private buffer sized by fa_b200_workspace_bytes is used
+    instead, so that the capture owns it."""
     P.force_kernel = _force_kernel
-    ws = None
-    need = lib.fa_b200_workspace_bytes(C.byref(P), op)
-    if need == C.c_size_t(-1).value:
-        check(-1)
-    if need:
-        ws = torch.empty(need, dtype=torch.uint8, device=device)
-        P.workspace, P.workspace_bytes = ws.data_ptr(), need
-    check(fn(C.byref(P), _stream(device)))
+    stream = _stream(device)
+    ref = C.byref(P)
+    if torch.cuda.is_current_stream_capturing():
+        need = lib.fa_b200_workspace_bytes(ref, op)
+        if need == C.c_size_t(-1).value:
+            check(-1)
+        ws = torch.empty(max(need, 16), dtype=torch.uint8, device=device)
+        P.workspace, P.workspace_bytes = ws.data_ptr(), ws.numel()
+        check(fn(ref, stream))
+    else:
+        key = (device.index, stream)
+        ws = _ws_cache.get(key)
+        if ws is not None:
+            P.workspace, P.workspace_bytes = ws.data_ptr(), ws.numel()
+        rc = fn(ref, stream)
+        if rc == _cabi.FA_ERR_WORKSPACE:
+            need = lib.fa_b200_workspace_bytes(ref, op)
+            if need == C.c_size_t(-1).value:
+                check(-1)
+            ws = torch.empty(max(2 * need, 1 << 20), dtype=torch.uint8, device=device)
+            _ws_cache[key] = ws
+            P.workspace, P.workspace_bytes = ws.data_ptr(), ws.numel()
+            rc = fn(ref, stream)
+        check(rc)
     last_call_info.update(kernel_used=P.kernel_used, num_splits=P.num_splits, launches=P.launches)
+
+
+class _on_device:
+    """`with torch.cuda.device(dev)` only when dev is not already current (the guard costs microseconds)."""
+    __slots__ = ("g",)
+
+    def __init__(self, dev):
+        self.g = None if torch.cuda.current_device() == dev.index else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.g is not None:
+            self.g.__enter__()
+
+    def __exit__(self, *a):
+        if self.g is not None:
+            self.g.__exit__(*a)
 
 
 def _pad_head(x, d_pad):
@@ -102,7 +141,7 @@ def fwd(q, k, v, out_, alibi_slopes_, p_dropout, softmax_scale, is_causal, windo
     else:
         out = torch.empty_like(q_p)
     lse = torch.empty((b, h, sq), dtype=torch.float32, device=q.device)
-    with torch.cuda.device(q.device):
+    with _on_device(q.device):
         if sk > 0 and sq > 0:
             P = FaFwdParams()
             P.q, P.k, P.v, P.o, P.softmax_lse = q_p.data_ptr(), k_p.data_ptr(), v_p.data_ptr(), out.data_ptr(), lse.data_ptr()
@@ -177,7 +216,7 @@ def varlen_fwd(q, k, v, out_, cu_seqlens_q, cu_seqlens_k, seqused_k, block_table
     lse = torch.empty((b, h, max_seqlen_q), dtype=torch.float32, device=dev)
     if zero_tensors:
         out.zero_(); lse.fill_(float("-inf"))
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         if max_seqlen_k > 0 and max_seqlen_q > 0 and total_q > 0:
             P = FaFwdParams()
             P.q, P.k, P.v, P.o, P.softmax_lse = q_p.data_ptr(), k_p.data_ptr(), v_p.data_ptr(), out.data_ptr(), lse.data_ptr()
@@ -281,7 +320,7 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
         _i32_dev(cache_batch_idx_, "cache_batch_idx", dev)
         _chk(cache_batch_idx_.is_contiguous() and tuple(cache_batch_idx_.shape) == (b,), "cache_batch_idx must have shape (batch_size)")
 
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         P = FaFwdParams()
         P.q, P.k, P.v, P.o, P.softmax_lse = q.data_ptr(), kcache.data_ptr(), vcache.data_ptr(), out.data_ptr(), lse.data_ptr()
         P.q_batch_stride, P.q_row_stride, P.q_head_stride = q.stride(0), q.stride(1), q.stride(2)
