@@ -23,7 +23,7 @@ K_TC5, K_TILE, K_DEC = 1, 2, 3
 
 def C(name, kern, kind="dense", **kw):
     d = dict(name=name, kern=kern, kind=kind, b=2, sq=256, sk=256, h=4, hk=4, d=128, dtype="bf16",
-             causal=False, window=(-1, -1), alibi=False, pmode="t", page=0, splits=0, seed=0, mixed=0.0, poison=False)
+             causal=False, window=(-1, -1), alibi=False, pmode="t", page=0, splits=0, seed=0, mixed=0.0, poison=False, grow=False)
     d.update(kw)
     return d
 
@@ -72,6 +72,9 @@ CASES += [
     C("tc5_varlen_paged256", K_TC5, kind="varlen", b=2, sq=300, sk=1000, page=256, h=4, hk=1, causal=True, poison=True),
     C("tc5_kvcache_paged16", K_TC5, kind="kvcache", b=2, sq=200, sk=900, page=16, h=8, hk=2, causal=True),
     C("tc5_kvcache_paged32_alibi", K_TC5, kind="kvcache", b=2, sq=150, sk=500, page=32, h=4, hk=4, causal=True, alibi=True),
+    # scores that keep growing along the keys: exercises the lazy-rescale / recompute branch of the prefill softmax
+    C("tc5_growing_scores", K_TC5, b=1, h=4, hk=2, sq=384, sk=2048, grow=True),
+    C("tc5_growing_scores_causal_fp16", K_TC5, b=2, h=2, hk=2, sq=1024, sk=1024, causal=True, dtype="fp16", grow=True),
     C("mixed_paged16", 0, kind="varlen", expect=K_TC5, b=8, sq=400, sk=900, page=16, h=8, hk=2, causal=True, mixed=0.6, poison=True),
     C("mixed_paged16_g8", 0, kind="varlen", expect=K_TC5, b=6, sq=300, sk=700, page=16, h=16, hk=2, causal=True, mixed=0.5, poison=True),
     C("mixed_dense_varlen", 0, kind="varlen", expect=K_TC5, b=7, sq=300, sk=600, h=8, hk=2, causal=True, mixed=0.5),
@@ -112,6 +115,8 @@ def run_case(spec):
         q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
         k = torch.randn(b, sk, hk, d, device=dev, dtype=dt)
         v = torch.randn(b, sk, hk, d, device=dev, dtype=dt)
+        if spec["grow"]:
+            k = (k.float() * torch.linspace(0.2, 6.0, sk, device=dev).view(1, sk, 1, 1)).to(dt)
         out, lse, _ = fa.flash_attn_func(q, k, v, causal=causal, window_size=window, alibi_slopes=slopes, return_attn_probs=True)
         bias = orc.attn_bias_from_alibi_slopes(slopes, sq, sk, causal=causal) if slopes is not None else None
         ref32, _ = orc.attention_ref(q, k, v, attn_bias=bias, causal=causal, window_size=window)
