@@ -240,3 +240,48 @@ def test_full_size_configs_vs_reference_kernel(cfg):
         valid = torch.arange(n, device=dev).view(1, 1, -1) < torch.tensor(lens, device=dev).view(-1, 1, 1)
         fin = fin & valid
     assert (lse[..., :n][fin] - rl[..., :n][fin]).abs().max() < 2e-3
+
+
+def _varlen_check(lens_q, lens_k, h=8, hk=2, d=128, causal=True, seed=0, tol_mult=2):
+    """flash_attn_varlen_func on explicit (possibly empty) sequence lengths vs the fp32 oracle."""
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import vllm_flash_attn_2_cuda as ext
+    torch.manual_seed(seed)
+    dev, dt = "cuda", torch.bfloat16
+    cu_q = torch.tensor([0] + list(torch.tensor(lens_q).cumsum(0)), dtype=torch.int32)
+    cu_k = torch.tensor([0] + list(torch.tensor(lens_k).cumsum(0)), dtype=torch.int32)
+    q = torch.randn(int(cu_q[-1]), h, d, device=dev, dtype=dt)
+    k = torch.randn(max(int(cu_k[-1]), 1), hk, d, device=dev, dtype=dt)[: int(cu_k[-1])]
+    v = torch.randn_like(k)
+    out = fa.flash_attn_varlen_func(q, k, v, cu_q.to(dev), cu_k.to(dev), max(lens_q), max(lens_k), causal=causal)
+    info = dict(ext.last_call_info)
+    ref32, _ = orc.attention_ref_varlen(q, k, v, cu_q, cu_k, causal=causal)
+    pt, _ = orc.attention_ref_varlen(q, k, v, cu_q, cu_k, causal=causal, upcast=False, reorder_ops=True)
+    err = (out.float() - ref32.float()).abs().max().item()
+    err_pt = (pt.float() - ref32.float()).abs().max().item()
+    assert not torch.isnan(out.float()).any()
+    assert err <= tol_mult * err_pt + 1e-5, (err, err_pt, info)
+    return info
+
+
+def test_varlen_empty_sequences_through_the_work_list():
+    """Zero-length q and/or k sequences inside a varlen batch (reference BlockInfo semantics,
+    src/block_info.h:11-42): no work unit for empty q, O = 0 for empty k; the batch is large enough
+    (> 148 units) that the persistent kernel runs from the device-built work list."""
+    info = _varlen_check([600, 0, 1, 257, 0, 128, 300, 513, 40], [600, 50, 700, 257, 0, 0, 300, 513, 900], h=16, hk=4)
+    assert info["kernel_used"] == 1 and info["launches"] == 3     # schedule + prefill + decode
+    info = _varlen_check([130, 0, 70], [130, 64, 0], h=4, hk=4, causal=False)
+    assert info["kernel_used"] == 1
+
+
+def test_varlen_many_sequences_mixed():
+    """1500 sequences (more than the schedule kernel's thread count), mostly short: single-token and
+    few-token sequences go to the decode kernel, the rest to the tcgen05 kernel, a handful of long ones
+    dominate the cost ordering."""
+    g = torch.Generator().manual_seed(5)
+    lens_q = torch.randint(1, 41, (1500,), generator=g).tolist()
+    lens_k = [x + int(y) for x, y in zip(lens_q, torch.randint(0, 200, (1500,), generator=g))]
+    for i, s in ((7, 1100), (400, 700), (1499, 300)):
+        lens_q[i] = s; lens_k[i] = s + 100
+    info = _varlen_check(lens_q, lens_k, h=8, hk=2, seed=1)
+    assert info["kernel_used"] == 1 and info["launches"] == 3
