@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 2
+#define FA_B200_ABI_VERSION 3
 
 enum {
   FA_OK = 0,
@@ -105,6 +105,10 @@ typedef struct FaFwdParams {
    * key in this shard — exactly the per-split partials of the reference's split-KV kernel
    * (flash_api.cpp:212-213, flash_fwd_kernel.h:513-552), ready for fa_b200_combine. */
   int32_t partial_out;
+  /* fwd_kvcache, sequence-sharded decode: the cache passed in holds keys [kv_shard_start,
+   * kv_shard_start + kv_shard_len) of every sequence and cache_seqlens are the GLOBAL lengths; the kernels
+   * use clamp(len - start, 0, kv_shard_len).  kv_shard_len = 0 disables it. */
+  int32_t kv_shard_start, kv_shard_len;
 
   /* ---- tuning / diagnostics ---- */
   int32_t num_sms;       /* 0 = query the device */
@@ -152,6 +156,31 @@ int fa_b200_append_kv(FaFwdParams* p, void* stream);
 int fa_b200_combine(const void* o_part, const float* lse_part, void* o, float* lse,
                     int32_t n, int64_t rows, int32_t d, int64_t part_stride, int64_t lse_stride,
                     int32_t part_dtype, int32_t out_dtype, void* stream);
+
+/* Cross-GPU merge of sequence-sharded decode partials in one kernel per rank (no reference analogue:
+ * the reference has no multi-GPU path; the algebra is combine_attn_seqk_parallel's,
+ * flash_fwd_kernel.h:1151-1221, lifted from splits to ranks).  Every rank pushes its packed fp32 record
+ * [o (b,h,seqlen_q,d) | lse (b,h,seqlen_q)] into all ranks' receive areas through peer-mapped pointers
+ * (NVLink stores), publishes a sequence number, waits for the peers' and LSE-combines.  recv[r] / flags[r]
+ * are rank r's receive area ([2][world][record_elems] fp32) and flag array ([world] uint32, zeroed once)
+ * as mapped into THIS process (e.g. torch symmetric memory buffer_ptrs); state is this rank's own
+ * {calls, ctas_done} pair (zeroed once).  All ranks must make the same sequence of calls. */
+#define FA_MAX_PEERS 8
+typedef struct FaExchangeParams {
+  void* recv[FA_MAX_PEERS];
+  uint32_t* flags[FA_MAX_PEERS];
+  const void* local_record;  /* this rank's record, 16-byte aligned */
+  uint32_t* state;
+  int32_t rank, world;
+  int32_t b, h, seqlen_q, d; /* d % 4 == 0 */
+  int64_t record_elems;      /* fp32 elements per slot: >= b*h*seqlen_q*(d+1), multiple of 4 */
+  void* o;                   /* (b,seqlen_q,h,d) by the strides below */
+  float* softmax_lse;        /* (b,h,seqlen_q) or NULL */
+  int64_t o_batch_stride, o_row_stride, o_head_stride;
+  int32_t out_dtype;         /* 0 = fp32, 1 = bf16, 2 = fp16 */
+} FaExchangeParams;
+int fa_b200_exchange_combine(const FaExchangeParams* p, void* stream);
+size_t fa_b200_exchange_params_size(void);
 
 #ifdef __cplusplus
 }

@@ -285,3 +285,28 @@ def test_varlen_many_sequences_mixed():
         lens_q[i] = s; lens_k[i] = s + 100
     info = _varlen_check(lens_q, lens_k, h=8, hk=2, seed=1)
     assert info["kernel_used"] == 1 and info["launches"] == 3
+
+
+def test_fused_exchange_single_rank_protocol():
+    """fa_b200_exchange_combine with world = 1 (plain allocation): the push / flag / parity protocol over
+    several consecutive calls, and the merge result against the ordinary kvcache call."""
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import sharded
+    torch.manual_seed(0)
+    dev, dt = torch.device("cuda", 0), torch.bfloat16
+    b, h, hk, d, page, ctx = 3, 8, 2, 128, 16, 2048
+    nblk = b * ctx // page
+    kc = torch.randn(nblk, page, hk, d, device=dev, dtype=dt); vc = torch.randn_like(kc)
+    bt = torch.randperm(nblk, device=dev).to(torch.int32).view(b, -1).contiguous()
+    lens = torch.tensor([ctx, 777, 0], dtype=torch.int32, device=dev)     # one empty sequence: O = 0, LSE = +inf
+    xch = sharded.PeerExchange(sharded.partial_record_numel(b, h, 1, d), dev)
+    for it in range(5):                                                   # parity flips every call
+        q = torch.randn(b, 1, h, d, device=dev, dtype=dt)
+        ref, lref = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=lens, block_table=bt, causal=True,
+                                                return_softmax_lse=True)
+        out, lse = sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=0, shard_end=ctx,
+                                                                causal=True, return_softmax_lse=True, exchange=xch)
+        assert (out.float() - ref.float()).abs().max().item() <= 4e-3, it
+        fin = torch.isfinite(lref)
+        assert (lse[fin] - lref[fin]).abs().max().item() < 1e-4 and bool((torch.isinf(lse) == torch.isinf(lref)).all())
+        assert bool((out[2] == 0).all())

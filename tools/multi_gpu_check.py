@@ -117,12 +117,23 @@ def main():
         del kfull, vfull
     ms = timed(f, a.iters, world, dev)
     ms_local = timed(lambda: sharded.kvcache_partial(q, kc, vc, sharded.seq_shard_lengths(lens, s, e), bt), a.iters, world, dev)
+    # fused exchange: peer-memory push + wait + combine in one kernel instead of NCCL all-gather + combine
+    xch = sharded.PeerExchange(sharded.partial_record_numel(b, 1, H, D), dev)
+    ff = lambda: sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e,
+                                                              causal=True, return_softmax_lse=True, exchange=xch)
+    out_f, lse_f = ff()
+    torch.cuda.synchronize()
+    err_f = (out_f.float() - out.float()).abs().max().item(); lerr_f = (lse_f - lse).abs().max().item()
+    ms_fused = timed(ff, a.iters, world, dev)
+    ms_fused_graph = timed_graph(ff, a.iters, world, dev)
     lens_shard = sharded.seq_shard_lengths(lens, s, e)
     ms_graph = timed_graph(f, a.iters, world, dev)
     ms_local_graph = timed_graph(lambda: sharded.kvcache_partial(q, kc, vc, lens_shard, bt), a.iters, world, dev)
     if rank == 0:
         nbytes = 2.0 * float(lens.sum().item()) * HK * D * 2
         print(json.dumps({"case": "C5_seq_sharded_decode", "n_gpus": world, "batch": b, "ctx": ctx, "ms": ms,
+                          "ms_fused_exchange": ms_fused, "ms_fused_exchange_cuda_graph": ms_fused_graph,
+                          "fused_vs_nccl_max_abs_diff": err_f, "fused_vs_nccl_lse_diff": lerr_f,
                           "ms_cuda_graph": ms_graph, "ms_local_kernel_only_cuda_graph": ms_local_graph,
                           "agg_GBps_cuda_graph": (nbytes / (ms_graph * 1e-3) / 1e9) if ms_graph else None,
                           "ms_local_kernel_only": ms_local, "agg_GBps": nbytes / (ms * 1e-3) / 1e9,

@@ -8,7 +8,7 @@ BUILD=${FA_BUILD_DIR:-build}
 OUT=${FA_OUT:-vllm_flash_attn/libfa_b200.so}
 mkdir -p $BUILD
 pids=()
-for f in fa_api fa_combine fa_append fa_decode fa_tile fa_prefill_tc5; do
+for f in fa_api fa_combine fa_append fa_decode fa_tile fa_prefill_tc5 fa_exchange; do
   if [ ! -f $BUILD/$f.o ] || [ -n "$(find csrc ../include -newer $BUILD/$f.o -type f | head -1)" ]; then
     ( $NVCC $FLAGS -Xptxas -v -c csrc/$f.cu -o $BUILD/$f.o > $BUILD/$f.log 2>&1 || { echo "FAILED $f"; tail -30 $BUILD/$f.log; exit 1; } ) &
     pids+=($!)

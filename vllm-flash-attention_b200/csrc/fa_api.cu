@@ -116,6 +116,8 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   k.seqlen_knew = a->seqlen_knew;   // rows already appended by fa_b200_append_kv
   k.lse_seq_stride = a->seqlen_q;
   k.min_rows = 0; k.max_rows = INT_MAX;
+  FA_CHECK(a->kv_shard_len >= 0 && a->kv_shard_start >= 0 && (a->kv_shard_len == 0 || op == OP_KVCACHE), "kv_shard_* is only valid for fwd_kvcache");
+  k.kv_shard_start = a->kv_shard_start; k.kv_shard_len = a->kv_shard_len;
   k.partial = 0;
   if (a->partial_out) {
     FA_CHECK(op == OP_KVCACHE, "partial_out is only valid for fwd_kvcache");
@@ -351,3 +353,22 @@ extern "C" int fa_b200_append_kv(FaFwdParams* a, void* stream) {
   if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in append kernel launch: %s", cudaGetErrorString(e));
   return FA_OK;
 }
+
+// Sequence-sharded decode: push + wait + LSE-combine across the GPUs of one box (csrc/fa_exchange.cu).
+extern "C" int fa_b200_exchange_combine(const FaExchangeParams* a, void* stream) {
+  g_err[0] = 0;
+  FA_CHECK(a != nullptr, "params is NULL");
+  FA_CHECK(a->world >= 1 && a->world <= FA_MAX_PEERS && a->rank >= 0 && a->rank < a->world, "bad rank/world");
+  FA_CHECK(a->b > 0 && a->h > 0 && a->seqlen_q > 0 && a->d > 0 && a->d % 4 == 0, "bad shape");
+  FA_CHECK(a->record_elems % 4 == 0 && a->record_elems >= (int64_t)a->b * a->h * a->seqlen_q * (a->d + 1), "record_elems too small or not a multiple of 4");
+  FA_CHECK(a->local_record && a->state && a->o, "NULL pointer");
+  FA_CHECK((reinterpret_cast<uintptr_t>(a->local_record) & 15) == 0, "local_record must be 16-byte aligned");
+  FA_CHECK(a->out_dtype >= 0 && a->out_dtype <= 2, "bad out_dtype");
+  for (int r = 0; r < a->world; r++)
+    FA_CHECK(a->recv[r] && a->flags[r] && (reinterpret_cast<uintptr_t>(a->recv[r]) & 15) == 0, "recv/flags pointer missing or misaligned");
+  FA_CHECK(a->o_row_stride % 4 == 0 && a->o_head_stride % 4 == 0 && a->o_batch_stride % 4 == 0, "output strides must be multiples of 4 elements");
+  cudaError_t e = launch_exchange_combine(*a, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in exchange kernel launch: %s", cudaGetErrorString(e));
+  return FA_OK;
+}
+extern "C" size_t fa_b200_exchange_params_size(void) { return sizeof(FaExchangeParams); }

@@ -35,6 +35,7 @@ struct KParams {
   int num_splits;
   int lse_seq_stride;                           // seqlen_q used for lse/accum row indexing
   int min_rows, max_rows;                        // serve only sequences with min_rows <= seqlen_q*group <= max_rows (mixed batches)
+  int kv_shard_start, kv_shard_len;               // sequence-sharded decode: this rank holds keys [start, start+len) of every sequence (len 0 = off)
   int2* work_items; int* work_header;           // tcgen05 prefill: cost-sorted (sequence, m_block) list + {draw counter, count}; NULL = static order
   long long* trace;                             // FA_TC5_TRACE builds only: per-event clock64 stamps of one CTA
   int partial;                                  // write fp32 partials (o_accum/lse_accum, -inf for empty rows) even with 1 split
@@ -69,6 +70,7 @@ struct SeqInfo {
       k_off = (int64_t)kv_batch * p.k_batch_stride; v_off = (int64_t)kv_batch * p.v_batch_stride;
     }
     if (p.seqused_k) sk = p.seqused_k[bidb];
+    if (p.kv_shard_len > 0) sk = min(max(sk - p.kv_shard_start, 0), p.kv_shard_len);   // global length -> keys held locally
   }
 };
 

@@ -1,0 +1,150 @@
+// fa_exchange.cu — cross-GPU merge of sequence-sharded decode partials in ONE kernel per rank:
+// push this rank's (out fp32 | lse) record into every peer's receive area with plain stores over
+// NVLink peer mappings, publish a sequence number, wait for the peers' numbers, LSE-combine.
+// Replaces "NCCL all-gather + combine launch" (two launches and a collective's latency) for the
+// long-context decode configuration; the algebra is combine_attn_seqk_parallel's
+// (reference src/flash_fwd_kernel.h:1151-1221) lifted from splits to ranks.
+//
+// Memory (all in a symmetric allocation, same layout on every rank; see vllm_flash_attn/sharded.py):
+//   recv[2][world][record]   receive area, double-buffered by call parity
+//   flags[world]             flags[r] = sequence number of the last record rank r has delivered here
+//   state[2]                 {calls completed, CTAs done pushing in the current call}
+// Protocol of call number n (n = state[0] + 1, read by every CTA before it pushes anything):
+//   1. every CTA copies its slice of the local record to recv[n&1][rank] of every rank (incl. self),
+//      fences system-wide and bumps state[1]; the CTA that completes the count resets it, sets
+//      state[0] = n and stores n into flags[rank] of every peer;
+//   2. every CTA waits until flags[r] >= n for all r, then merges its rows from recv[n&1][*].
+// A rank cannot run two calls ahead of a peer (its call n+1 needs the peer's flag n+1, sent only
+// after the peer finished call n), so two receive buffers suffice.  All state lives in device memory:
+// the launch is CUDA-graph replayable.  The wait is bounded (trap after ~4 s) so that a missing peer
+// surfaces as a launch failure, not a hung GPU.
+#include "fa_common.cuh"
+#include "fa_launch.h"
+
+namespace fa {
+
+struct ExchangeParams {
+  float* recv[FA_MAX_PEERS];
+  unsigned* flags[FA_MAX_PEERS];
+  const float* local;       // this rank's record [o (rows*d) | lse (rows)]
+  unsigned* state;
+  int rank, world;
+  int b, h, sq, d;
+  int64_t record;           // fp32 elements per record slot (>= rows*(d+1), multiple of 4)
+  void* o; float* lse;      // outputs: o (b,sq,h,d) by strides, lse (b,h,sq) or NULL
+  int64_t o_batch_stride, o_row_stride, o_head_stride;
+  int out_dtype;            // 0 fp32, 1 bf16, 2 fp16
+};
+
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(256) fa_exchange_combine_kernel(const __grid_constant__ ExchangeParams p) {
+  __shared__ unsigned s_n;
+  if (threadIdx.x == 0) s_n = ld_acquire_sys(p.state) + 1u;   // read before this CTA pushes: the count cannot complete yet
+  __syncthreads();
+  const unsigned n = s_n;
+  const int64_t rows = (int64_t)p.b * p.h * p.sq;
+  const int64_t used = rows * (p.d + 1);                      // fp32 elements actually carried
+  const int64_t vec = (used + 3) / 4;                         // 16-byte pieces (record is padded to 16 B)
+  const int64_t slot = ((int64_t)(n & 1u) * p.world + p.rank) * p.record;
+
+  // ---- 1. push ----
+  const float4* src = reinterpret_cast<const float4*>(p.local);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < vec; i += (int64_t)gridDim.x * blockDim.x) {
+    const float4 v = src[i];
+    for (int r = 0; r < p.world; r++) reinterpret_cast<float4*>(p.recv[r] + slot)[i] = v;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned done = atomicAdd(p.state + 1, 1u);
+    if (done == gridDim.x - 1) {                              // all CTAs of this rank have pushed and fenced
+      p.state[1] = 0u;
+      __threadfence_system();
+      for (int r = 0; r < p.world; r++) st_release_sys(p.flags[r] + p.rank, n);
+      st_release_sys(p.state, n);
+    }
+    // ---- 2. wait for every rank's record of call n ----
+    long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (int r = 0; r < p.world; r++) {
+      while ((int)(ld_acquire_sys(p.flags[p.rank] + r) - n) < 0) {
+        long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > 4000000000ll) __trap();
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- 3. merge: one warp per row ----
+  const float* base = p.recv[p.rank] + (int64_t)(n & 1u) * p.world * p.record;
+  const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
+  for (int64_t row = (int64_t)blockIdx.x * warps + (threadIdx.x >> 5); row < rows; row += (int64_t)gridDim.x * warps) {
+    float ls[FA_MAX_PEERS], mx = -INFINITY;
+#pragma unroll
+    for (int r = 0; r < FA_MAX_PEERS; r++) {
+      ls[r] = r < p.world ? __ldcg(base + r * p.record + rows * p.d + row) : -INFINITY;
+      mx = fmaxf(mx, ls[r]);
+    }
+    const bool empty = mx == -INFINITY;
+    float sum = 0.f;
+#pragma unroll
+    for (int r = 0; r < FA_MAX_PEERS; r++) sum += empty ? 0.f : expf(ls[r] - mx);
+    const float lse = empty ? INFINITY : logf(sum) + mx;      // rows without any key: O = 0, LSE = +inf
+    float w[FA_MAX_PEERS];
+#pragma unroll
+    for (int r = 0; r < FA_MAX_PEERS; r++) w[r] = empty ? 0.f : expf(ls[r] - lse);
+    const int qi = (int)(row % p.sq), hi = (int)((row / p.sq) % p.h), bi = (int)(row / ((int64_t)p.sq * p.h));
+    const int64_t o_off = (int64_t)bi * p.o_batch_stride + (int64_t)qi * p.o_row_stride + (int64_t)hi * p.o_head_stride;
+    for (int c = lane * 4; c < p.d; c += 128) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < FA_MAX_PEERS; r++) {
+        if (r < p.world) {
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(base + r * p.record + row * p.d + c));
+          acc.x += w[r] * v.x; acc.y += w[r] * v.y; acc.z += w[r] * v.z; acc.w += w[r] * v.w;
+        }
+      }
+      if (p.out_dtype == 0) {
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.o) + o_off + c) = acc;
+      } else if (p.out_dtype == 1) {
+        uint2 pk; pk.x = Pack2<__nv_bfloat16>::pack(acc.x, acc.y); pk.y = Pack2<__nv_bfloat16>::pack(acc.z, acc.w);
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.o) + o_off + c) = pk;
+      } else {
+        uint2 pk; pk.x = Pack2<__half>::pack(acc.x, acc.y); pk.y = Pack2<__half>::pack(acc.z, acc.w);
+        *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(p.o) + o_off + c) = pk;
+      }
+    }
+    if (p.lse && lane == 0) p.lse[row] = lse;
+  }
+}
+
+cudaError_t launch_exchange_combine(const FaExchangeParams& a, cudaStream_t stream) {
+  ExchangeParams p;
+  for (int r = 0; r < FA_MAX_PEERS; r++) {
+    p.recv[r] = r < a.world ? reinterpret_cast<float*>(a.recv[r]) : nullptr;
+    p.flags[r] = r < a.world ? a.flags[r] : nullptr;
+  }
+  p.local = reinterpret_cast<const float*>(a.local_record); p.state = a.state;
+  p.rank = a.rank; p.world = a.world; p.b = a.b; p.h = a.h; p.sq = a.seqlen_q; p.d = a.d; p.record = a.record_elems;
+  p.o = a.o; p.lse = a.softmax_lse;
+  p.o_batch_stride = a.o_batch_stride; p.o_row_stride = a.o_row_stride; p.o_head_stride = a.o_head_stride;
+  p.out_dtype = a.out_dtype;
+  const int64_t rows = (int64_t)a.b * a.h * a.seqlen_q;
+  // every CTA has to be resident while it waits for the peers: keep the grid far below one wave
+  int grid = (int)((rows + 7) / 8);
+  if (grid > 64) grid = 64;
+  if (grid < 1) grid = 1;
+  fa_exchange_combine_kernel<<<grid, 256, 0, stream>>>(p);
+  return cudaGetLastError();
+}
+
+}  // namespace fa

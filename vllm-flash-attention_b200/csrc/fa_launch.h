@@ -1,5 +1,6 @@
 // fa_launch.h — host-side launch entry points of the kernels (one per .cu file).
 #pragma once
+#include "fa_b200.h"
 #include <cuda_runtime.h>
 #include "fa_common.cuh"
 
@@ -64,6 +65,7 @@ cudaError_t launch_append(const AppendParams& a, bool is_bf16, cudaStream_t stre
 bool tc5_supported(const KParams& p);
 cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, int num_sms,
                                cudaStream_t stream);
+cudaError_t launch_exchange_combine(const FaExchangeParams& a, cudaStream_t stream);
 size_t tc5_workspace_bytes(const KParams& p, int64_t total_q, int num_sms);
 
 }  // namespace fa

@@ -24,7 +24,7 @@ from typing import Callable, Optional, Tuple
 import torch
 
 __all__ = ["head_shard", "seq_shard_range", "seq_shard_lengths", "partial_record_numel",
-           "kvcache_partial", "merge_partials", "flash_attn_with_kvcache_seq_sharded"]
+           "kvcache_partial", "merge_partials", "flash_attn_with_kvcache_seq_sharded", "PeerExchange"]
 
 
 # --------------------------------------------------------------------------------------------
@@ -65,10 +65,12 @@ def partial_record_numel(b: int, h: int, sq: int, d: int) -> int:
 # compute steps (CUDA kernels through the C ABI)
 def kvcache_partial(q, k_cache, v_cache, cache_seqlens, block_table=None, *, softmax_scale=None,
                     causal=False, window_size=(-1, -1), alibi_slopes=None, num_splits=0,
-                    buf: Optional[torch.Tensor] = None):
+                    buf: Optional[torch.Tensor] = None, shard: Optional[Tuple[int, int]] = None):
     """Attention of q against ONE SHARD of the KV sequence: returns (buf, out32, lse) where `buf` is
     the packed fp32 record (see partial_record_numel), out32 its (b,h,sq,d) view and lse its (b,h,sq)
-    view, with lse = -inf for rows that see no key in this shard."""
+    view, with lse = -inf for rows that see no key in this shard.  With shard=(start, end) the
+    cache holds keys [start, end) of every sequence and `cache_seqlens` are the GLOBAL lengths (the
+    kernels clamp them: no extra launches)."""
     from . import vllm_flash_attn_2_cuda as ext
     b, sq, h, d = q.shape
     if buf is None:
@@ -78,7 +80,7 @@ def kvcache_partial(q, k_cache, v_cache, cache_seqlens, block_table=None, *, sof
         softmax_scale = d ** -0.5
     out32, lse = ext.fwd_kvcache(q, k_cache, v_cache, None, None, cache_seqlens, None, None, None, block_table,
                                  alibi_slopes, None, softmax_scale, causal, window_size[0], window_size[1],
-                                 True, num_splits, _partial_buf=buf[:rec])
+                                 True, num_splits, _partial_buf=buf[:rec], _kv_shard=shard)
     return buf, out32, lse
 
 
@@ -99,15 +101,84 @@ def merge_partials(records: torch.Tensor, b: int, h: int, sq: int, d: int, out_d
 
 
 # --------------------------------------------------------------------------------------------
+class PeerExchange:
+    """Peer-memory state for the fused cross-GPU merge (fa_b200_exchange_combine): one symmetric
+    allocation per rank — receive area [2][world][record], flag array [world], state [2], and the local
+    staging record the decode kernel writes — mapped into every process of the box by torch symmetric
+    memory (NVLink P2P).  Create it once (collectively, all ranks of `group`) for the largest
+    (b, h, seqlen_q, d) that will be merged; `merge()` then costs one kernel launch per decode step and
+    is CUDA-graph replayable.  All ranks must call merge() the same number of times."""
+
+    def __init__(self, max_record_elems: int, device, group=None):
+        import torch.distributed as dist
+        single = not dist.is_initialized() or dist.get_world_size(group) == 1
+        self.group = None if single else (group if group is not None else dist.group.WORLD)
+        self.world = 1 if single else dist.get_world_size(self.group)
+        self.rank = 0 if single else dist.get_rank(self.group)
+        if self.world > 8:
+            raise ValueError("PeerExchange supports at most 8 ranks (one NVSwitch box)")
+        self.record = (max_record_elems + 3) // 4 * 4
+        recv_elems = 2 * self.world * self.record
+        self.off_flags = recv_elems                       # fp32/uint32 element offsets inside the allocation
+        self.off_state = self.off_flags + 16
+        self.off_local = self.off_state + 16
+        total = self.off_local + self.record
+        if single:                                        # one rank: an ordinary allocation, same protocol
+            self.buf = torch.zeros(total, dtype=torch.float32, device=device)
+            self.handle = None
+            self.ptrs = [self.buf.data_ptr()]
+        else:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.buf = symm_mem.empty(total, dtype=torch.float32, device=device)
+            self.buf.zero_()
+            self.handle = symm_mem.rendezvous(self.buf, self.group)
+            torch.cuda.synchronize(device)
+            self.handle.barrier()                         # every rank's flags/state are zero before any push
+            self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        self.local_record = self.buf[self.off_local:self.off_local + self.record]
+
+    def merge(self, b: int, h: int, sq: int, d: int, out_dtype: torch.dtype, rec_elems: Optional[int] = None):
+        """LSE-merge the records all ranks have staged in `local_record` (layout of
+        partial_record_numel).  Returns (out (b,sq,h,d) out_dtype, lse (b,h,sq) fp32)."""
+        from ._cabi import FaExchangeParams, check, lib
+        import ctypes as C
+        rec = rec_elems or partial_record_numel(b, h, sq, d)
+        if rec > self.record:
+            raise ValueError(f"record of {rec} fp32 exceeds the PeerExchange capacity {self.record}")
+        dev = self.buf.device
+        out = torch.empty((b, sq, h, d), dtype=out_dtype, device=dev)
+        lse = torch.empty((b, h, sq), dtype=torch.float32, device=dev)
+        P = FaExchangeParams()
+        for r in range(self.world):
+            P.recv[r] = self.ptrs[r]
+            P.flags[r] = self.ptrs[r] + 4 * self.off_flags
+        P.local_record = self.ptrs[self.rank] + 4 * self.off_local
+        P.state = self.ptrs[self.rank] + 4 * self.off_state
+        P.rank, P.world = self.rank, self.world
+        P.b, P.h, P.seqlen_q, P.d = b, h, sq, d
+        P.record_elems = self.record
+        P.o, P.softmax_lse = out.data_ptr(), lse.data_ptr()
+        P.o_batch_stride, P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
+        P.out_dtype = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}[out_dtype]
+        check(lib.fa_b200_exchange_combine(C.byref(P), torch.cuda.current_stream(dev).cuda_stream))
+        return out, lse
+
+
+# --------------------------------------------------------------------------------------------
 def flash_attn_with_kvcache_seq_sharded(q, k_cache, v_cache, cache_seqlens, block_table=None, *,
                                         shard_start: int, shard_end: int, group=None, softmax_scale=None,
                                         causal=False, alibi_slopes=None, num_splits=0, return_softmax_lse=False,
+                                        exchange: Optional["PeerExchange"] = None,
                                         _local_fn: Optional[Callable] = None, _merge_fn: Optional[Callable] = None):
     """Decode attention with the KV sequence sharded over the ranks of `group`.
 
     q (b, seqlen_q, h, d) is replicated.  This rank's k_cache/v_cache (+ block_table) hold keys
     [shard_start, shard_end) of every sequence (local row 0 = global key shard_start; see
     seq_shard_range); `cache_seqlens` are the GLOBAL lengths.  Every rank returns the full result.
+
+    With `exchange` (a PeerExchange created once for the group) the records travel by peer-memory
+    stores inside ONE fused push + wait + combine kernel instead of an NCCL all-gather followed by a
+    combine launch.
 
     seqlen_q must be 1 (or causal=False): with the last query token every key of the sequence is
     visible, so no cross-rank mask is needed.  ALiBi is rejected because its bias
@@ -120,14 +191,22 @@ def flash_attn_with_kvcache_seq_sharded(q, k_cache, v_cache, cache_seqlens, bloc
     if alibi_slopes is not None:
         raise RuntimeError("sequence-sharded attention does not support ALiBi")
     world = dist.get_world_size(group) if dist.is_initialized() else 1
-    local_lens = seq_shard_lengths(cache_seqlens, shard_start, shard_end)
+    shard = (shard_start, shard_end)
     rec = partial_record_numel(b, h, sq, d)
+    if exchange is not None:
+        if _local_fn is not None:
+            _local_fn(exchange.local_record[:rec])
+        else:
+            kvcache_partial(q, k_cache, v_cache, cache_seqlens, block_table, softmax_scale=softmax_scale, causal=False,
+                            num_splits=num_splits, buf=exchange.local_record[:rec], shard=shard)
+        out, lse = exchange.merge(b, h, sq, d, q.dtype, rec)
+        return (out, lse) if return_softmax_lse else out
     gathered = torch.empty((world, rec), dtype=torch.float32, device=q.device)
     rank = dist.get_rank(group) if world > 1 else 0
     mine = gathered[rank]                       # the local kernel writes straight into its slot
-    local = _local_fn or (lambda buf: kvcache_partial(q, k_cache, v_cache, local_lens, block_table,
+    local = _local_fn or (lambda buf: kvcache_partial(q, k_cache, v_cache, cache_seqlens, block_table,
                                                        softmax_scale=softmax_scale, causal=False,
-                                                       num_splits=num_splits, buf=buf))
+                                                       num_splits=num_splits, buf=buf, shard=shard))
     local(mine)
     if world > 1:
         # ONE collective: every rank's (out fp32 | lse) record, in place (slot r of `gathered`)

@@ -258,7 +258,7 @@ def varlen_fwd(q, k, v, out_, cu_seqlens_q, cu_seqlens_k, seqused_k, block_table
 
 def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_, cache_batch_idx_,
                 block_table_, alibi_slopes_, out_, softmax_scale, is_causal, window_size_left,
-                window_size_right, is_rotary_interleaved, num_splits, *, _partial_buf=None) -> List[torch.Tensor]:
+                window_size_right, is_rotary_interleaved, num_splits, *, _partial_buf=None, _kv_shard=None) -> List[torch.Tensor]:
     """mha_fwd_kvcache (flash_api.cpp:671-937).  q (b,sq,h,d); cache (b_c,sk,hk,d) or paged
     (num_blocks,page,hk,d) with block_table (b,max_blocks); optional new k/v (b,sk_new,hk,d) appended
     in place at cache_seqlens (with rotary on k and q).  Returns [out, softmax_lse].
@@ -331,6 +331,8 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
             P.partial_out = 1
         else:
             P.o_batch_stride, P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
+        if _kv_shard is not None:           # (start, end): the cache holds that key range, seqlens_k are global
+            P.kv_shard_start, P.kv_shard_len = int(_kv_shard[0]), int(_kv_shard[1] - _kv_shard[0])
         P.b, P.seqlen_q, P.seqlen_k, P.h, P.h_k, P.d = b, sq, sk, h, hk, d
         P.is_bf16 = int(q.dtype == torch.bfloat16)
         P.softmax_scale = softmax_scale
