@@ -183,14 +183,17 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
     const int page = PAGED ? p.page_block_size : TC5_BN;
     const int box_rows = min(page, TC5_BN), nbox = TC5_BN / box_rows;
     int ring = 0;                 // K/V ring cursor, runs on across work units
-    int published = 0;
-    for (int wi = 0;; wi++) {
-      int w = 0;
-      if (p.work_items) { if (lane == 0) w = atomicAdd(p.work_header, 1); w = __shfl_sync(0xffffffffu, w, 0); }
-      else w = wi * gridDim.x + ((wi & 1) ? gridDim.x - 1 - blockIdx.x : blockIdx.x);   // boustrophedon
+    int published = 0, fetches = 0;
+    // next live work unit: drawn from the sorted list, or decoded arithmetically (static order)
+    auto fetch = [&]() {
       Tc5Work wk;
-      wk.valid = w < total;
-      if (wk.valid) {
+      for (;;) {
+        int w = 0;
+        if (p.work_items) { if (lane == 0) w = atomicAdd(p.work_header, 1); w = __shfl_sync(0xffffffffu, w, 0); }
+        else w = fetches * gridDim.x + ((fetches & 1) ? gridDim.x - 1 - blockIdx.x : blockIdx.x);   // boustrophedon
+        fetches++;
+        wk.valid = w < total;
+        if (!wk.valid) break;
         const int unit = w / p.h;
         wk.head = w - unit * p.h;
         if (p.work_items) { const int2 it = p.work_items[unit]; wk.bidb = it.x; wk.m_block = it.y; }
@@ -200,8 +203,11 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
         wk.q_row0 = p.cu_seqlens_q ? p.cu_seqlens_q[wk.bidb] : 0;
         wk.k_row0 = (!PAGED && p.cu_seqlens_k) ? p.cu_seqlens_k[wk.bidb] : 0;
         const int rows = wk.sq * p.group;
-        if (wk.m_block * 2 * TC5_BM >= wk.sq || rows < p.min_rows || rows > p.max_rows) continue;   // static mode only
+        if (wk.m_block * 2 * TC5_BM < wk.sq && rows >= p.min_rows && rows <= p.max_rows) break;   // dead units: static order only
       }
+      return wk;
+    };
+    auto publish = [&](const Tc5Work& wk) {
       const int ms = published & 1;
       if (lane == 0) {
         mbar_wait(bar_w_empty + 8 * ms, ((published >> 1) & 1) ^ 1);
@@ -210,7 +216,14 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
         mbar_arrive(bar_w_full + 8 * ms);
       }
       published++;
-      if (!wk.valid) break;
+    };
+    // The mailbox runs one unit ahead of the loads: unit u+1 is drawn and published before the loads of
+    // unit u are issued, so the other roles never wait for the scheduler at a unit boundary.
+    Tc5Work wk = fetch();
+    publish(wk);
+    for (int unit_idx = 0; wk.valid; unit_idx++) {
+      const Tc5Work nxt = fetch();
+      publish(nxt);
 
       const int m0 = wk.m_block * 2 * TC5_BM, sq = wk.sq, sk = wk.sk;
       const int kvh = wk.head / p.group;
@@ -221,7 +234,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
       if (lane == 0) {
         for (int t = 0; t < 2; t++) {
           // both Q barriers flip once per work unit (inactive tile: plain arrive), so their parity is the unit's
-          mbar_wait(bar_q_empty + 8 * t, (published & 1));      // the previous unit's last QK_t has read Q_t
+          mbar_wait(bar_q_empty + 8 * t, (unit_idx & 1) ^ 1);   // the previous unit's last QK_t has read Q_t
           if (!(t == 0 ? act0 : act1)) { mbar_arrive(bar_q + 8 * t); continue; }
           mbar_expect_tx(bar_q + 8 * t, Cfg::TILE_BYTES);
           for (int c = 0; c < ND; c++)
@@ -293,6 +306,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
           }
         }
       }
+      wk = nxt;
     }
     __syncwarp();
   } else if (warp == TC5_MMA_WARP) {
