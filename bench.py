@@ -184,7 +184,9 @@ def run_reference(args):
     line = {"impl": "reference", "metric": "attn_fwd_tflops_prefill", "value": val, "unit": "TFLOP/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "C2 Llama-3-8B prefill varlen causal GQA 32q/8kv D=128 (bounded sample per step)"},
+            "config": {"workload": "C2 Llama-3-8B prefill: flash_attn_varlen_func causal GQA 32q/8kv D=128, 16384 tokens, "
+                                   "seqlens " + str(SEQLENS_C2),
+                       "sample": "each step = a bounded sample of that workload on the host cores: " + desc},
             "cpu_baseline": {"value": val, "unit": "TFLOP/s", "cores": threads, "kind": "port", "sample": desc},
             "e2e": {"value": val, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
