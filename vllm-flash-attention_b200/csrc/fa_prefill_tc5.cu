@@ -46,7 +46,7 @@ constexpr int TC5_THREADS = 384;       // 3 warpgroups; warps 10-11 idle (setmax
 constexpr int TC5_REGS_SOFTMAX = 224, TC5_REGS_OTHER = 56;
 constexpr int TC5_PRODUCER_WARP = 8, TC5_MMA_WARP = 9;
 
-struct Tc5Maps { CUtensorMap q, k, v; };
+struct Tc5Maps { CUtensorMap q, k, v, o; };   // o: 64 x 1 x 32 x 1 box (one warp's epilogue slab)
 template <typename T> struct IsBf16 { static constexpr bool value = false; };
 template <> struct IsBf16<__nv_bfloat16> { static constexpr bool value = true; };
 
@@ -60,7 +60,7 @@ template <int D> struct Tc5Cfg {
   static constexpr int OFF_BAR = OFF_KV + NS * TILE_BYTES;
   static constexpr int NUM_BARS = 4 /*q full,empty*/ + 2 * NS + 2 /*s*/ + 2 /*p*/ + 2 /*o*/ + 4 /*mailbox full,empty*/;
   static constexpr int OFF_MBOX = OFF_BAR + NUM_BARS * 8 + 16;      // after the TMEM base slot; 2 x 32 B
-  static constexpr int OFF_STAGE = OFF_MBOX + 64;                   // epilogue staging: 8 softmax warps x 4 KB
+  static constexpr int OFF_STAGE = (OFF_MBOX + 64 + 1023) / 1024 * 1024;   // epilogue staging: 8 softmax warps x 4 KB, TMA-store sources (1024 B aligned)
   static constexpr int SMEM = OFF_STAGE + 8 * 4096 + 1024;          // +1024: manual alignment
   static constexpr int TM_S = 0, TM_O = 256;                // TMEM column bases; tile t adds t*128
 };
@@ -155,7 +155,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
 
   // ---- one-time setup ----
   if (warp == TC5_PRODUCER_WARP && lane == 0) {
-    prefetch_tmap(&maps.q); prefetch_tmap(&maps.k); prefetch_tmap(&maps.v);
+    prefetch_tmap(&maps.q); prefetch_tmap(&maps.k); prefetch_tmap(&maps.v); prefetch_tmap(&maps.o);
     for (int t = 0; t < 2; t++) {
       mbar_init(bar_q + 8 * t, 1); mbar_init(bar_q_empty + 8 * t, 1);
       mbar_init(bar_s + 8 * t, 1); mbar_init(bar_p + 8 * t, 128); mbar_init(bar_o + 8 * t, 1);
@@ -602,7 +602,8 @@ cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, 
   Tc5Maps maps;
   const bool varlen = p.cu_seqlens_q != nullptr;
   const int64_t q_rows = varlen ? total_q : p.seqlen_q;
-  bool ok = make_map(&maps.q, p.q, is_bf16, TC5_BM, p.d, p.h, q_rows, varlen ? 1 : p.b, p.q_head_stride, p.q_row_stride, p.q_batch_stride);
+  bool ok = make_map(&maps.q, p.q, is_bf16, TC5_BM, p.d, p.h, q_rows, varlen ? 1 : p.b, p.q_head_stride, p.q_row_stride, p.q_batch_stride) &&
+            make_map(&maps.o, p.o, is_bf16, 32, p.d, p.h, q_rows, varlen ? 1 : p.b, p.o_head_stride, p.o_row_stride, p.o_batch_stride);
   if (p.block_table) {   // (d, heads, row in page, block)
     const int box = p.page_block_size < TC5_BN ? p.page_block_size : TC5_BN;
     ok = ok && make_map(&maps.k, p.k, is_bf16, box, p.d, p.h_k, p.page_block_size, p.num_blocks, p.k_head_stride, p.k_row_stride, p.k_batch_stride) &&
