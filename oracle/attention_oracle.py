@@ -275,6 +275,6 @@ def attention_ref_varlen(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, wind
             # kernel convention: causal ALiBi bias is slope*j (csrc/flash_attn/src/mask.h:181), the
             # test helper's is slope*(j-(sk-1)) (tests/test_flash_attn.py:38-39): same out, LSE
             # differs by the row-constant slope*(sk-1)
-            l_i = l_i + sl.float().view(-1, 1).cpu() * (k1 - k0 - 1)
+            l_i = l_i + sl.float().view(-1, 1).to(l_i.device) * (k1 - k0 - 1)
         lse[i, :, :q1 - q0] = l_i
     return out, lse

@@ -21,3 +21,12 @@ def pytest_collection_modifyitems(config, items):
     for it in items:
         if "gpu" in it.keywords:
             it.add_marker(skip)
+
+
+@pytest.fixture(autouse=True)
+def _unpinned_kernel_choice():
+    """Tests that pin a kernel family (ext._force_kernel) must not leak the pin into the next test."""
+    yield
+    mod = sys.modules.get("vllm_flash_attn.vllm_flash_attn_2_cuda")
+    if mod is not None:
+        mod._force_kernel = 0

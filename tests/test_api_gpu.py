@@ -37,7 +37,13 @@ def test_auto_dispatch_picks_expected_kernels():
     assert _ext().last_call_info["kernel_used"] == 3          # decode
     q2 = torch.randn(1, 200, 4, 96, device=dev, dtype=dt); k2 = torch.randn_like(q2)
     fa.flash_attn_func(q2, k2, k2)
-    assert _ext().last_call_info["kernel_used"] == 2          # tile kernel (d=96)
+    assert _ext().last_call_info["kernel_used"] == 1          # tcgen05 prefill (d=96 in the D=128 instantiation)
+    q3 = torch.randn(1, 200, 4, 160, device=dev, dtype=dt); k3 = torch.randn_like(q3)
+    fa.flash_attn_func(q3, k3, k3)
+    assert _ext().last_call_info["kernel_used"] == 2          # tile kernel (d > 128 prefill)
+    q4 = torch.randn(2, 1, 8, 192, device=dev, dtype=dt); k4 = torch.randn(2, 300, 2, 192, device=dev, dtype=dt)
+    fa.flash_attn_with_kvcache(q4, k4, k4)
+    assert _ext().last_call_info["kernel_used"] == 3          # decode, every head dim of the reference build
 
 
 def test_c1_full_and_out_argument():
@@ -310,3 +316,29 @@ def test_fused_exchange_single_rank_protocol():
         fin = torch.isfinite(lref)
         assert (lse[fin] - lref[fin]).abs().max().item() < 1e-4 and bool((torch.isinf(lse) == torch.isinf(lref)).all())
         assert bool((out[2] == 0).all())
+
+
+def test_varlen_seqused_k():
+    """varlen_fwd(seqused_k=...) (flash_api.cpp:428,:553-556; BlockInfo src/block_info.h:24): keys beyond
+    seqused_k[b] are ignored although cu_seqlens_k spans them.  Prefill rows run on the tcgen05 kernel,
+    the single-token sequence on the decode kernel."""
+    ext = _ext()
+    torch.manual_seed(3)
+    dev, dt, h, hk, d = "cuda", torch.bfloat16, 8, 2, 128
+    lens_q, lens_k, used = [300, 1, 200], [500, 400, 350], [420, 333, 200]
+    cu_q = torch.tensor([0] + lens_q).cumsum(0).to(torch.int32); cu_k = torch.tensor([0] + lens_k).cumsum(0).to(torch.int32)
+    q = torch.randn(sum(lens_q), h, d, device=dev, dtype=dt)
+    k = torch.randn(sum(lens_k), hk, d, device=dev, dtype=dt); v = torch.randn_like(k)
+    su = torch.tensor(used, dtype=torch.int32, device=dev)
+    res = ext.varlen_fwd(q, k, v, None, cu_q.to(dev), cu_k.to(dev), su, None, None, max(lens_q), max(lens_k), 0.0,
+                         d ** -0.5, False, True, -1, -1, False, None)
+    out = res[0]
+    assert ext.last_call_info["kernel_used"] == 1 and ext.last_call_info["launches"] == 2
+    # oracle: the same batch with k, v physically cut to the used lengths
+    kc = torch.cat([k[int(cu_k[i]):int(cu_k[i]) + used[i]] for i in range(3)])
+    vc = torch.cat([v[int(cu_k[i]):int(cu_k[i]) + used[i]] for i in range(3)])
+    cu_u = torch.tensor([0] + used).cumsum(0).to(torch.int32)
+    ref32, _ = orc.attention_ref_varlen(q, kc, vc, cu_q, cu_u, causal=True)
+    pt, _ = orc.attention_ref_varlen(q, kc, vc, cu_q, cu_u, causal=True, upcast=False, reorder_ops=True)
+    err, err_pt = (out.float() - ref32.float()).abs().max().item(), (pt.float() - ref32.float()).abs().max().item()
+    assert err <= 2 * err_pt + 1e-5, (err, err_pt)

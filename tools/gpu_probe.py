@@ -79,6 +79,22 @@ CASES += [
     C("mixed_paged16_g8", 0, kind="varlen", expect=K_TC5, b=6, sq=300, sk=700, page=16, h=16, hk=2, causal=True, mixed=0.5, poison=True),
     C("mixed_dense_varlen", 0, kind="varlen", expect=K_TC5, b=7, sq=300, sk=600, h=8, hk=2, causal=True, mixed=0.5),
     C("mixed_paged_d64", 0, kind="varlen", expect=K_TC5, b=5, sq=260, sk=520, page=32, d=64, h=8, hk=8, causal=True, mixed=0.4, poison=True),
+    # head dims 96 / 32 through the tcgen05 kernel (D = 128 / 64 instantiation, TMA boxes clipped at the true width)
+    C("tc5_d96_causal", K_TC5, sq=500, sk=700, d=96, causal=True, h=6, hk=2),
+    C("tc5_d96_dense_fp16", K_TC5, sq=384, sk=384, d=96, dtype="fp16"),
+    C("tc5_d32_local_fp16", K_TC5, sq=300, sk=450, d=32, dtype="fp16", window=(70, 20), h=6, hk=3),
+    C("tc5_d32_causal", K_TC5, sq=256, sk=256, d=32, causal=True),
+    C("tc5_d96_varlen_paged16", K_TC5, kind="varlen", b=3, sq=300, sk=700, d=96, page=16, h=8, hk=2, causal=True, poison=True),
+    C("tc5_d96_varlen_alibi", K_TC5, kind="varlen", b=4, sq=280, sk=280, d=96, h=4, hk=4, causal=True, alibi=True),
+    C("tc5_d128_varlen_alibi", K_TC5, kind="varlen", b=4, sq=280, sk=280, d=128, h=4, hk=4, causal=True, alibi=True),
+    C("mixed_paged16_d96", 0, kind="varlen", expect=K_TC5, b=7, sq=300, sk=700, d=96, page=16, h=12, hk=4, causal=True, mixed=0.5, poison=True),
+    # every head dim of the reference build through the decode kernel
+    C("dec_d32", K_DEC, kind="kvcache", b=3, sq=1, sk=600, d=32, h=8, hk=2, page=16, causal=True),
+    C("dec_d96_paged16", K_DEC, kind="kvcache", b=3, sq=1, sk=1000, d=96, h=12, hk=4, page=16, causal=True),
+    C("dec_d96_rows32_split", K_DEC, kind="kvcache", b=1, sq=4, sk=5000, d=96, h=16, hk=2, causal=True),
+    C("dec_d160", K_DEC, kind="kvcache", b=2, sq=1, sk=700, d=160, h=8, hk=1, page=32, dtype="fp16"),
+    C("dec_d192_local", K_DEC, kind="kvcache", b=2, sq=2, sk=500, d=192, h=4, hk=2, window=(100, 0)),
+    C("dec_d224_alibi", K_DEC, kind="kvcache", b=2, sq=1, sk=400, d=224, h=4, hk=4, alibi=True, causal=True),
 ]
 
 
@@ -230,6 +246,7 @@ def run_case(spec):
         fin = torch.isfinite(lref)
         res["lse_err"] = (lse[fin] - lref[fin]).abs().max().item()
     res.update(ext.last_call_info)
+    ext._force_kernel = 0
     torch.cuda.synchronize()
     res["ok"] = bool((not res["nan"]) and res["err"] <= 2 * res["err_pt"] + 1e-4 and res["lse_err"] < 2e-3)
     return res

@@ -289,22 +289,32 @@ static cudaError_t launch_decode_t(const KParams& p, cudaStream_t stream) {
 
 template <typename T>
 static cudaError_t launch_decode_d(const KParams& p, int mt, cudaStream_t stream) {
-  if (p.d == 64) {
-    if (mt == 1) return launch_decode_t<T, 64, 1, 4, 6>(p, stream);
-    if (mt == 2) return launch_decode_t<T, 64, 2, 4, 6>(p, stream);
-  } else if (p.d == 128) {
-    if (mt == 1) return launch_decode_t<T, 128, 1, 4, 3>(p, stream);
-    if (mt == 2) return launch_decode_t<T, 128, 2, 4, 3>(p, stream);
-  } else if (p.d == 256) {
-    if (mt == 1) return launch_decode_t<T, 256, 1, 4, 3>(p, stream);
+  // ring depth: about 24 KB of K+V in flight per warp
+#define FA_DEC_CASE(D_, ST_)                                                         \
+  case D_:                                                                           \
+    if (mt == 1) return launch_decode_t<T, D_, 1, 4, ST_>(p, stream);                \
+    if constexpr (D_ <= 128) { if (mt == 2) return launch_decode_t<T, D_, 2, 4, ST_>(p, stream); } \
+    break;
+  switch (p.d) {
+    FA_DEC_CASE(32, 8)
+    FA_DEC_CASE(64, 6)
+    FA_DEC_CASE(96, 4)
+    FA_DEC_CASE(128, 3)
+    FA_DEC_CASE(160, 3)
+    FA_DEC_CASE(192, 3)
+    FA_DEC_CASE(224, 3)
+    FA_DEC_CASE(256, 3)
+    default: break;
   }
+#undef FA_DEC_CASE
   return cudaErrorInvalidValue;
 }
 
+// Every head dimension of the reference build (multiples of 32 up to 256, static_switch.h:80-107):
+// up to 32 packed rows while the O fragment fits the register file (d <= 128), 16 above.
 bool decode_supported(int d, int rows) {
-  if (d == 64 || d == 128) return rows <= 32;
-  if (d == 256) return rows <= 16;
-  return false;
+  if (d < 32 || d > 256 || d % 32 != 0) return false;
+  return rows <= (d <= 128 ? 32 : 16);
 }
 
 cudaError_t launch_decode(const KParams& p, bool is_bf16, cudaStream_t stream) {

@@ -282,7 +282,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
               for (int idx = lane; idx < (TC5_BN - r_begin) * ND * 8; idx += 32) {
                 const int ch = idx & 7, c = (idx >> 3) % ND, r = r_begin + (idx >> 3) / ND;
                 uint4 val = make_uint4(0, 0, 0, 0);
-                if (r < valid) {
+                if (r < valid && c * 64 + ch * 8 < p.d) {
                   const int g = row0 + r, pg = g / page;
                   const int blk = table[min(pg, p.max_blocks_per_seq - 1)];
                   val = *reinterpret_cast<const uint4*>(vbase + (int64_t)blk * p.v_batch_stride +
@@ -320,7 +320,11 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
     // draining: the first QK of the next unit is issued right behind the last PV of this one, so
     // S is ready when a softmax warpgroup returns from its epilogue.
     constexpr uint32_t idesc_qk = make_idesc(IS_BF16, TC5_BM, TC5_BN, false);
-    constexpr uint32_t idesc_pv = make_idesc(IS_BF16, TC5_BM, D, true);
+    // head dims 32 / 96 run in the D = 64 / 128 instantiation: the TMA boxes clip (zero-fill) at the
+    // tensor's true width, QK^T takes d/16 k-steps and PV is issued with N = d, so no tensor-pipe
+    // cycle is spent on the padding columns
+    const uint32_t idesc_pv = make_idesc(IS_BF16, TC5_BM, p.d, true);
+    const int nks = p.d >> 4;
     // descriptor = constant high part | (smem address >> 4); the k-step loops are NOT unrolled: one MMA
     // occupies the tensor pipe for 64 clk, so a few scalar instructions per issue are free, and the
     // issuer's 56 registers hold no precomputed descriptor tables (spills would sit on the P -> PV chain)
@@ -361,6 +365,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
           const uint32_t qa = ((q_sm + t * Cfg::TILE_BYTES) & 0x3FFFF) >> 4, kb = ((kv_sm + slot * Cfg::TILE_BYTES) & 0x3FFFF) >> 4;
 #pragma unroll
           for (int ks = 0; ks < D / 16; ks++) {
+            if (ks >= nks) break;                       // d = 96 / 32 stop early
             const uint32_t off = (ks >> 2) * (Cfg::SUB_BYTES >> 4) + (ks & 3) * 2;
             umma_ss(tmem + Cfg::TM_S + t * 128, DESC_KMAJOR | (qa + off), DESC_KMAJOR | (kb + off), idesc_qk, ks > 0);
           }
@@ -527,8 +532,8 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, int box_rows, 
 }
 
 bool tc5_supported(const KParams& p) {
-  if (p.d != 64 && p.d != 128) return false;
-  if (p.cache_batch_idx || p.seqused_k) return false;
+  if (p.d != 32 && p.d != 64 && p.d != 96 && p.d != 128) return false;
+  if (p.cache_batch_idx) return false;
   if (p.num_splits > 1) return false;
   if (p.block_table) {
     // paged K/V: a 128-key tile must be a whole number of pages, or a page a whole number of tiles
@@ -624,8 +629,8 @@ cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, 
     if (e != cudaSuccess) return e;
     grid = num_sms;
   }
-  if (is_bf16) return p.d == 64 ? launch_tc5_d<__nv_bfloat16, 64>(p, maps, grid, stream) : launch_tc5_d<__nv_bfloat16, 128>(p, maps, grid, stream);
-  return p.d == 64 ? launch_tc5_d<__half, 64>(p, maps, grid, stream) : launch_tc5_d<__half, 128>(p, maps, grid, stream);
+  if (is_bf16) return p.d <= 64 ? launch_tc5_d<__nv_bfloat16, 64>(p, maps, grid, stream) : launch_tc5_d<__nv_bfloat16, 128>(p, maps, grid, stream);
+  return p.d <= 64 ? launch_tc5_d<__half, 64>(p, maps, grid, stream) : launch_tc5_d<__half, 128>(p, maps, grid, stream);
 }
 
 }  // namespace fa
