@@ -49,6 +49,9 @@ def main():
             x = [ev(wg, it, i) for i in (6, 7, 8)]
             if x[0]:
                 print(f"        WG{wg} unit end after it {it}: PV(last) done @{x[0]-t00}, epilogue stores +{x[1]-x[0]}, next unit read +{x[2]-x[1]}")
+            pw = [ev(wg, it, 9 + w) - t00 for w in range(4)]
+            sw = [e[1]] + [ev(wg, it, 12 + w) - t00 for w in (1, 2, 3)]
+            print(f"        WG{wg} per warp: S seen {sw}  P published {pw}  (softmax time {[pw[w] - sw[w] for w in range(4)]})")
             print(f"it {it:3d} WG{wg}: wait@{e[0]:7d} S_ready +{e[1]-e[0]:5d} ld1 +{e[2]-e[1]:4d} max +{e[3]-e[2]:4d} "
                   f"exp_half +{e[4]-e[3]:5d} P_pub +{e[5]-e[4]:5d}  | iter total {e[5]-e[0]:5d}  S_ready@{e[1]:7d} P_hi@{e[5]:7d}")
         m = [ev(2, it, i) - t00 for i in range(16)]
