@@ -290,20 +290,49 @@ static cudaError_t launch_decode_t(const KParams& p, cudaStream_t stream) {
 template <typename T>
 static cudaError_t launch_decode_d(const KParams& p, int mt, cudaStream_t stream) {
   // ring depth: about 24 KB of K+V in flight per warp
-#define FA_DEC_CASE(D_, ST_)                                                         \
+// small head dims move few bytes per 16-key chunk, so they need more warps per SM to cover the per-chunk
+// latency chain (measured on B200, batch 256 x ctx 4096: d=64 4.97 -> 6.25 TB/s, d=32 3.48 -> 4.41 TB/s going
+// from 4 to 8 warps per CTA at the same shared-memory footprint)
+#ifndef FA_DEC32_NW
+#define FA_DEC32_NW 8
+#define FA_DEC32_ST 4
+#endif
+#ifndef FA_DEC64_NW
+#define FA_DEC64_NW 8
+#define FA_DEC64_ST 3
+#endif
+#ifndef FA_DEC96_NW
+#define FA_DEC96_NW 8
+#define FA_DEC96_ST 2
+#endif
+#ifndef FA_DEC160_ST
+#define FA_DEC160_ST 2      // 2 stages: two CTAs per SM instead of one (d=160 4.72 -> 6.68 TB/s, d=192 5.83 -> 6.82 TB/s)
+#define FA_DEC192_ST 2
+#endif
+#ifndef FA_DEC224_NW
+#define FA_DEC224_NW 6      // one CTA per SM either way: 6 warps x 2 stages beat 4 x 3 (d=224 5.98 -> 6.46, d=256 6.64 -> 6.91 TB/s)
+#define FA_DEC224_ST 2
+#define FA_DEC256_NW 6
+#define FA_DEC256_ST 2
+#endif
+#ifndef FA_DEC128_NW
+#define FA_DEC128_NW 4
+#define FA_DEC128_ST 3
+#endif
+#define FA_DEC_CASE(D_, NW_, ST_)                                                    \
   case D_:                                                                           \
-    if (mt == 1) return launch_decode_t<T, D_, 1, 4, ST_>(p, stream);                \
-    if constexpr (D_ <= 128) { if (mt == 2) return launch_decode_t<T, D_, 2, 4, ST_>(p, stream); } \
+    if (mt == 1) return launch_decode_t<T, D_, 1, NW_, ST_>(p, stream);              \
+    if constexpr (D_ <= 128) { if (mt == 2) return launch_decode_t<T, D_, 2, NW_, ST_>(p, stream); } \
     break;
   switch (p.d) {
-    FA_DEC_CASE(32, 8)
-    FA_DEC_CASE(64, 6)
-    FA_DEC_CASE(96, 4)
-    FA_DEC_CASE(128, 3)
-    FA_DEC_CASE(160, 3)
-    FA_DEC_CASE(192, 3)
-    FA_DEC_CASE(224, 3)
-    FA_DEC_CASE(256, 3)
+    FA_DEC_CASE(32, FA_DEC32_NW, FA_DEC32_ST)
+    FA_DEC_CASE(64, FA_DEC64_NW, FA_DEC64_ST)
+    FA_DEC_CASE(96, FA_DEC96_NW, FA_DEC96_ST)
+    FA_DEC_CASE(128, FA_DEC128_NW, FA_DEC128_ST)
+    FA_DEC_CASE(160, 4, FA_DEC160_ST)
+    FA_DEC_CASE(192, 4, FA_DEC192_ST)
+    FA_DEC_CASE(224, FA_DEC224_NW, FA_DEC224_ST)
+    FA_DEC_CASE(256, FA_DEC256_NW, FA_DEC256_ST)
     default: break;
   }
 #undef FA_DEC_CASE
