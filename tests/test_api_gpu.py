@@ -40,7 +40,11 @@ def test_auto_dispatch_picks_expected_kernels():
     assert _ext().last_call_info["kernel_used"] == 1          # tcgen05 prefill (d=96 in the D=128 instantiation)
     q3 = torch.randn(1, 200, 4, 160, device=dev, dtype=dt); k3 = torch.randn_like(q3)
     fa.flash_attn_func(q3, k3, k3)
-    assert _ext().last_call_info["kernel_used"] == 2          # tile kernel (d > 128 prefill)
+    assert _ext().last_call_info["kernel_used"] == 1          # tcgen05 prefill, one-tile units (d > 128)
+    kc3 = torch.randn(3, 400, 4, 160, device=dev, dtype=dt)
+    fa.flash_attn_with_kvcache(q3, kc3, kc3, cache_seqlens=torch.tensor([300], dtype=torch.int32, device=dev),
+                               cache_batch_idx=torch.tensor([2], dtype=torch.int32, device=dev))
+    assert _ext().last_call_info["kernel_used"] == 2          # tile kernel (cache_batch_idx with many query rows)
     q4 = torch.randn(2, 1, 8, 192, device=dev, dtype=dt); k4 = torch.randn(2, 300, 2, 192, device=dev, dtype=dt)
     fa.flash_attn_with_kvcache(q4, k4, k4)
     assert _ext().last_call_info["kernel_used"] == 3          # decode, every head dim of the reference build

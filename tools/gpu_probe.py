@@ -88,6 +88,16 @@ CASES += [
     C("tc5_d96_varlen_alibi", K_TC5, kind="varlen", b=4, sq=280, sk=280, d=96, h=4, hk=4, causal=True, alibi=True),
     C("tc5_d128_varlen_alibi", K_TC5, kind="varlen", b=4, sq=280, sk=280, d=128, h=4, hk=4, causal=True, alibi=True),
     C("mixed_paged16_d96", 0, kind="varlen", expect=K_TC5, b=7, sq=300, sk=700, d=96, page=16, h=12, hk=4, causal=True, mixed=0.5, poison=True),
+    # head dims above 128 through the tcgen05 kernel's one-tile-per-unit mode (D = 256 instantiation)
+    C("tc5_d256_causal", K_TC5, sq=700, sk=700, d=256, causal=True, h=4, hk=2),
+    C("tc5_d256_dense_fp16", K_TC5, sq=384, sk=512, d=256, dtype="fp16", h=2, hk=1),
+    C("tc5_d192_local", K_TC5, sq=500, sk=800, d=192, window=(150, 40), h=4, hk=2),
+    C("tc5_d160_causal_sq_gt_sk", K_TC5, sq=600, sk=250, d=160, causal=True, h=2, hk=2),
+    C("tc5_d224_alibi", K_TC5, sq=300, sk=300, d=224, causal=True, alibi=True, h=4, hk=4),
+    C("tc5_d256_varlen_paged16", K_TC5, kind="varlen", b=3, sq=300, sk=700, d=256, page=16, h=4, hk=2, causal=True, poison=True),
+    C("tc5_d192_varlen", K_TC5, kind="varlen", b=5, sq=400, sk=400, d=192, h=6, hk=2, causal=True),
+    C("tc5_d256_growing_scores", K_TC5, b=1, h=2, hk=2, sq=256, sk=1536, d=256, grow=True),
+    C("mixed_paged16_d256", 0, kind="varlen", expect=K_TC5, b=6, sq=300, sk=600, d=256, page=16, h=8, hk=2, causal=True, mixed=0.5, poison=True),
     # every head dim of the reference build through the decode kernel
     C("dec_d32", K_DEC, kind="kvcache", b=3, sq=1, sk=600, d=32, h=8, hk=2, page=16, causal=True),
     C("dec_d96_paged16", K_DEC, kind="kvcache", b=3, sq=1, sk=1000, d=96, h=12, hk=4, page=16, causal=True),

@@ -157,7 +157,7 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
       // A varlen batch may mix prompts with single-token (or few-token) sequences — vLLM's chunked
       // prefill.  Those would waste a 256-row tile per head, so they are routed to the decode
       // kernel (one CTA per KV head, K/V read once per group) by a second launch over the same batch.
-      if (op == OP_VARLEN && decode_supported(a->d, k.group)) pl->decode_rows = 32;
+      if (op == OP_VARLEN && decode_supported(a->d, k.group)) pl->decode_rows = a->d <= 128 ? 32 : 16;   // the decode kernel's row capacity
     } else kernel = FA_KERNEL_TILE;
   }
   if (kernel == FA_KERNEL_DECODE) FA_CHECK(decode_supported(a->d, rows), "decode kernel: d/rows not supported");

@@ -54,14 +54,19 @@ template <int D> struct Tc5Cfg {
   static constexpr int ND = D / 64;                         // 64-element (128 B) sub-tiles per row
   static constexpr int SUB_BYTES = 128 * 128;               // 128 rows x 128 B
   static constexpr int TILE_BYTES = ND * SUB_BYTES;         // a Q / K / V tile
-  static constexpr int NS = D == 128 ? 4 : 8;
+  // Q tiles per work unit.  d <= 128: two 128-row tiles ping-pong through the tensor core.  128 < d <= 256
+  // (D = 256): O alone takes 256 TMEM columns, so a unit is ONE 128-row tile (softmax warpgroup 1 stays idle),
+  // Q + one K + one V tile (64 KB each) fill shared memory and the K/V ring is 2 slots deep.
+  static constexpr int TILES = D > 128 ? 1 : 2;
+  static constexpr int UNIT_ROWS = TILES * 128;
+  static constexpr int NS = D == 256 ? 2 : (D == 128 ? 4 : 8);
   static constexpr int OFF_Q = 0;
-  static constexpr int OFF_KV = 2 * TILE_BYTES;
+  static constexpr int OFF_KV = TILES * TILE_BYTES;
   static constexpr int OFF_BAR = OFF_KV + NS * TILE_BYTES;
   static constexpr int NUM_BARS = 4 /*q full,empty*/ + 2 * NS + 2 /*s*/ + 2 /*p*/ + 2 /*o*/ + 4 /*mailbox full,empty*/;
   static constexpr int OFF_MBOX = OFF_BAR + NUM_BARS * 8 + 16;      // after the TMEM base slot; 2 x 32 B
-  static constexpr int OFF_STAGE = (OFF_MBOX + 64 + 1023) / 1024 * 1024;   // epilogue staging: 8 softmax warps x 4 KB, TMA-store sources (1024 B aligned)
-  static constexpr int SMEM = OFF_STAGE + 8 * 4096 + 1024;          // +1024: manual alignment
+  static constexpr int OFF_STAGE = (OFF_MBOX + 64 + 1023) / 1024 * 1024;   // epilogue staging: 4 KB per active softmax warp, TMA-store sources (1024 B aligned)
+  static constexpr int SMEM = OFF_STAGE + 4 * TILES * 4096 + 1024;  // +1024: manual alignment
   static constexpr int TM_S = 0, TM_O = 256;                // TMEM column bases; tile t adds t*128
 };
 
@@ -117,7 +122,10 @@ __device__ __forceinline__ TileRange tc5_range(const KParams& p, int r0, int sq,
   return t;
 }
 
-// One unit of work = 256 query rows (two 128-row tiles) of one (sequence, head).  The producer
+// Query rows per work unit: two 128-row tiles up to d = 128, one above (Tc5Cfg::TILES).
+__host__ __device__ constexpr int tc5_unit_rows(int d) { return d > 128 ? TC5_BM : 2 * TC5_BM; }
+
+// One unit of work = 256 (d > 128: 128) query rows of one (sequence, head).  The producer
 // warp decodes it and publishes it to the other roles through a 2-deep shared-memory mailbox.
 struct Tc5Work { int valid, head, bidb, m_block, sq, sk, q_row0, k_row0; };
 
@@ -178,7 +186,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
     // Work order: p.work_items (built by tc5_schedule_kernel, most expensive first) drawn through a
     // global counter — longest-processing-time-first list scheduling over the persistent CTAs — or,
     // for launches too small to need it, a static decode of (m_block, batch, head).
-    const int n_mb = (p.seqlen_q + 2 * TC5_BM - 1) / (2 * TC5_BM);
+    const int n_mb = (p.seqlen_q + Cfg::UNIT_ROWS - 1) / Cfg::UNIT_ROWS;
     const int total = p.work_items ? p.work_header[1] * p.h : n_mb * p.b * p.h;
     const int page = PAGED ? p.page_block_size : TC5_BN;
     const int box_rows = min(page, TC5_BN), nbox = TC5_BN / box_rows;
@@ -203,7 +211,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
         wk.q_row0 = p.cu_seqlens_q ? p.cu_seqlens_q[wk.bidb] : 0;
         wk.k_row0 = (!PAGED && p.cu_seqlens_k) ? p.cu_seqlens_k[wk.bidb] : 0;
         const int rows = wk.sq * p.group;
-        if (wk.m_block * 2 * TC5_BM < wk.sq && rows >= p.min_rows && rows <= p.max_rows) break;   // dead units: static order only
+        if (wk.m_block * Cfg::UNIT_ROWS < wk.sq && rows >= p.min_rows && rows <= p.max_rows) break;   // dead units: static order only
       }
       return wk;
     };
@@ -225,9 +233,9 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
       const Tc5Work nxt = fetch();
       publish(nxt);
 
-      const int m0 = wk.m_block * 2 * TC5_BM, sq = wk.sq, sk = wk.sk;
+      const int m0 = wk.m_block * Cfg::UNIT_ROWS, sq = wk.sq, sk = wk.sk;
       const int kvh = wk.head / p.group;
-      const TileRange tr0 = tc5_range(p, m0, sq, sk), tr1 = tc5_range(p, m0 + TC5_BM, sq, sk);
+      const TileRange tr0 = tc5_range(p, m0, sq, sk), tr1 = Cfg::TILES > 1 ? tc5_range(p, m0 + TC5_BM, sq, sk) : TileRange{0, 0};
       const bool act0 = tr0.je > tr0.jb, act1 = tr1.je > tr1.jb;
       const int j_begin = act0 ? (act1 ? min(tr0.jb, tr1.jb) : tr0.jb) : tr1.jb;
       const int j_end = act0 || act1 ? max(tr0.je, tr1.je) : j_begin;
@@ -354,8 +362,8 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
         }
 #endif
         if (!wk.valid) break;
-        const int m0 = wk.m_block * 2 * TC5_BM;
-        const TileRange tr0 = tc5_range(p, m0, wk.sq, wk.sk), tr1 = tc5_range(p, m0 + TC5_BM, wk.sq, wk.sk);
+        const int m0 = wk.m_block * Cfg::UNIT_ROWS;
+        const TileRange tr0 = tc5_range(p, m0, wk.sq, wk.sk), tr1 = Cfg::TILES > 1 ? tc5_range(p, m0 + TC5_BM, wk.sq, wk.sk) : TileRange{0, 0};
         const bool act0 = tr0.je > tr0.jb, act1 = tr1.je > tr1.jb;
         const int j_begin = act0 ? (act1 ? min(tr0.jb, tr1.jb) : tr0.jb) : tr1.jb;
         const int j_end = act0 || act1 ? max(tr0.je, tr1.je) : j_begin;
@@ -453,15 +461,17 @@ tc5_schedule_kernel(const __grid_constant__ KParams p, int2* items, int* header,
   const int tid = threadIdx.x;
   for (int i = tid; i < TC5_SCHED_BINS; i += TC5_SCHED_THREADS) bins[i] = 0;
   __syncthreads();
+  const int unit_rows = tc5_unit_rows(p.d);
   auto cost_of = [&](int mb, int sq, int sk) {
-    const TileRange a = tc5_range(p, mb * 2 * TC5_BM, sq, sk), b = tc5_range(p, mb * 2 * TC5_BM + TC5_BM, sq, sk);
+    const TileRange a = tc5_range(p, mb * unit_rows, sq, sk);
+    const TileRange b = unit_rows > TC5_BM ? tc5_range(p, mb * unit_rows + TC5_BM, sq, sk) : TileRange{0, 0};
     return min((a.je - a.jb) + (b.je - b.jb), TC5_SCHED_BINS - 1);
   };
   auto live = [&](int sq) { const int rows = sq * p.group; return sq > 0 && rows >= p.min_rows && rows <= p.max_rows; };
   for (int s = tid; s < p.b; s += TC5_SCHED_THREADS) {
     const SeqInfo si(p, s);
     if (!live(si.sq)) continue;
-    const int n = (si.sq + 2 * TC5_BM - 1) / (2 * TC5_BM);
+    const int n = (si.sq + unit_rows - 1) / unit_rows;
     for (int mb = 0; mb < n; mb++) atomicAdd(&bins[TC5_SCHED_BINS - 1 - cost_of(mb, si.sq, si.sk)], 1);   // bin 0 = most expensive
   }
   __syncthreads();
@@ -488,7 +498,7 @@ tc5_schedule_kernel(const __grid_constant__ KParams p, int2* items, int* header,
   for (int s = tid; s < p.b; s += TC5_SCHED_THREADS) {
     const SeqInfo si(p, s);
     if (!live(si.sq)) continue;
-    const int n = (si.sq + 2 * TC5_BM - 1) / (2 * TC5_BM);
+    const int n = (si.sq + unit_rows - 1) / unit_rows;
     for (int mb = 0; mb < n; mb++) {
       const int pos = atomicAdd(&bins[TC5_SCHED_BINS - 1 - cost_of(mb, si.sq, si.sk)], 1);
       if (pos < max_items) items[pos] = make_int2(s, mb);
@@ -532,7 +542,7 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, int box_rows, 
 }
 
 bool tc5_supported(const KParams& p) {
-  if (p.d != 32 && p.d != 64 && p.d != 96 && p.d != 128) return false;
+  if (p.d < 32 || p.d > 256 || p.d % 32 != 0) return false;   // every head dim of the reference build
   if (p.cache_batch_idx) return false;
   if (p.num_splits > 1) return false;
   if (p.block_table) {
@@ -571,7 +581,7 @@ static cudaError_t launch_tc5_d(const KParams& p, const Tc5Maps& maps, int grid,
 
 // Upper bound on the number of (sequence, m_block) work units, from host-side shapes only.
 int64_t tc5_max_units(const KParams& p, int64_t total_q) {
-  const int64_t per = 2 * TC5_BM;
+  const int64_t per = tc5_unit_rows(p.d);
   return p.cu_seqlens_q ? total_q / per + p.b : (int64_t)p.b * ((p.seqlen_q + per - 1) / per);
 }
 // Workspace for the cost-sorted work list; 0 when the launch is small enough for the static order.
@@ -629,8 +639,10 @@ cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, 
     if (e != cudaSuccess) return e;
     grid = num_sms;
   }
-  if (is_bf16) return p.d <= 64 ? launch_tc5_d<__nv_bfloat16, 64>(p, maps, grid, stream) : launch_tc5_d<__nv_bfloat16, 128>(p, maps, grid, stream);
-  return p.d <= 64 ? launch_tc5_d<__half, 64>(p, maps, grid, stream) : launch_tc5_d<__half, 128>(p, maps, grid, stream);
+  if (is_bf16) return p.d <= 64 ? launch_tc5_d<__nv_bfloat16, 64>(p, maps, grid, stream)
+                    : p.d <= 128 ? launch_tc5_d<__nv_bfloat16, 128>(p, maps, grid, stream) : launch_tc5_d<__nv_bfloat16, 256>(p, maps, grid, stream);
+  return p.d <= 64 ? launch_tc5_d<__half, 64>(p, maps, grid, stream)
+       : p.d <= 128 ? launch_tc5_d<__half, 128>(p, maps, grid, stream) : launch_tc5_d<__half, 256>(p, maps, grid, stream);
 }
 
 }  // namespace fa

@@ -17,7 +17,9 @@
 namespace fa {
 
 template <int D> struct TileCfg {
-  static constexpr int BM = 64, BN = 64, NW = 4;
+  // d >= 192: 64-key tiles would leave room for one CTA per SM only (160 KB at d=256); 32-key tiles keep two
+  // (measured: d=256 causal 184 -> 232 TFLOP/s, d=192 160 -> 205)
+  static constexpr int BM = 64, BN = D >= 192 ? 32 : 64, NW = 4;
   static constexpr int Q_BYTES = BM * D * 2;
   static constexpr int KV_BYTES = BN * D * 2;
   static constexpr int SMEM = Q_BYTES + 4 * KV_BYTES;   // K,V x 2 stages
