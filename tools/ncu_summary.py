@@ -1,6 +1,6 @@
 """Summarise an .ncu-rep (raw page) into the handful of metrics the roofline discussion needs.
   python tools/ncu_summary.py gpurun_out/prof.ncu-rep [extra_regex] [--traffic KEY]
---traffic KEY records dram read+write bytes of the first kernel in profiles/traffic.json under KEY
+--traffic KEY records dram read+write bytes of the longest captured launch in profiles/traffic.json under KEY
 (bench.py reports it as roofline.traffic)."""
 import csv, io, json, os, re, subprocess, sys
 argv = sys.argv[1:]
@@ -25,7 +25,9 @@ for r in rows[2:]:
             print(f"  {h} [{u}] = {v}")
 
 if traffic_key and len(rows) > 2:
-    r = rows[2]
+    # the longest captured launch is the benchmark's (warm-up / self-check launches of the same kernel are tiny)
+    ti = hdr.index("gpu__time_duration.sum")
+    r = max(rows[2:], key=lambda x: float(x[ti].replace(",", "")) * {"us": 1, "ms": 1e3, "ns": 1e-3, "s": 1e6}.get(units[ti].lower(), 1))
     def val(name):
         i = hdr.index(name)
         v, u = float(r[i].replace(",", "")), units[i].lower()
