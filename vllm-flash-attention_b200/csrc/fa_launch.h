@@ -61,7 +61,7 @@ struct AppendParams {
 };
 cudaError_t launch_append(const AppendParams& a, bool is_bf16, cudaStream_t stream);
 
-// fa_prefill_tc5.cu — tcgen05/TMA/TMEM prefill kernel, d in {64,128}.
+// fa_prefill_tc5.cu — tcgen05/TMA/TMEM prefill kernel, every head dim 32..256 (multiples of 32).
 bool tc5_supported(const KParams& p);
 cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, int num_sms,
                                cudaStream_t stream);

@@ -20,6 +20,9 @@
 // the first 64 columns of S_t (all of S_t is in registers by then).
 // MMA order:  QK0(0) QK1(0) { PV0(j) QK0(j+1) PV1(j) QK1(j+1) }  — while warpgroup 0 works on
 // S0(j+1) the tensor core runs PV1(j) and QK1(j+1).
+// Head dims: instantiations D = 64 / 128 / 256 serve d = 32,64 / 96,128 / 160..256 (d is a run-time value:
+// TMA boxes clip at the true width, QK^T takes d/16 k-steps, PV has N = d).  D = 256 runs ONE Q tile per
+// work unit (O0 = [256,512), warpgroup 1 idle, 2-slot K/V ring of 64 KB tiles) — see Tc5Cfg::TILES.
 #include "fa_common.cuh"
 #include "fa_sm100.cuh"
 #include <algorithm>

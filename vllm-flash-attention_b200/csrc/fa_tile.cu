@@ -4,7 +4,7 @@
 // src/flash_fwd_kernel.h:27-470, and compute_attn_1rowblock_splitkv, :474-1053): dense / varlen /
 // paged KV / cache_batch_idx / seqused_k, causal / sliding window / ALiBi, MHA/GQA/MQA, split-KV,
 // head dims 32..256 (multiples of 32, flash_api.cpp:135-137), fp16 / bf16.  It is the safety net
-// under the two B200-specialised kernels: fa_prefill_tc5.cu (tcgen05, d in {64,128}) takes the
+// under the two B200-specialised kernels: fa_prefill_tc5.cu (tcgen05, all head dims) takes the
 // compute-bound prefill shapes and fa_decode.cu the HBM-bound decode shapes.
 //
 // One CTA = 64 query rows of one (sequence, head[, split]); each warp owns 16 rows and walks the
