@@ -66,11 +66,15 @@ template <int D> struct Tc5Cfg {
   static constexpr int OFF_Q = 0;
   static constexpr int OFF_KV = TILES * TILE_BYTES;
   static constexpr int OFF_BAR = OFF_KV + NS * TILE_BYTES;
-  static constexpr int NUM_BARS = 4 /*q full,empty*/ + 2 * NS + 2 /*s*/ + 2 /*p*/ + 2 /*o*/ + 4 /*mailbox full,empty*/;
+  static constexpr int NUM_BARS = 4 /*q full,empty*/ + 2 * NS + 2 /*s*/ + 2 /*p*/ + 2 /*o*/ + 4 /*mailbox full,empty*/ + 2 /*q in TMEM (+pad)*/;
   static constexpr int OFF_MBOX = OFF_BAR + NUM_BARS * 8 + 16;      // after the TMEM base slot; 2 x 32 B
   static constexpr int OFF_STAGE = (OFF_MBOX + 64 + 1023) / 1024 * 1024;   // epilogue staging: 4 KB per active softmax warp, TMA-store sources (1024 B aligned)
   static constexpr int SMEM = OFF_STAGE + 4 * TILES * 4096 + 1024;  // +1024: manual alignment
   static constexpr int TM_S = 0, TM_O = 256;                // TMEM column bases; tile t adds t*128
+  // One-tile units (D = 256): the S1 region holds Q as a TMEM A operand (column x = elements 2x, 2x+1 of the
+  // row).  QK^T from shared memory needs the full 128 B/clk of shared-memory bandwidth (4 KB of Q + 4 KB of K
+  // per 64-clk MMA) and stalls whenever the K/V TMA writes of the next tile land; with Q in TMEM it needs half.
+  static constexpr int TM_Q = 128;
 };
 
 // exp2 of 32 scaled scores -> 16 packed bf16/fp16 pairs + row-sum accumulation.
@@ -157,7 +161,8 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
   const uint32_t bar_o = bar_p + 16;              // [2] PV_t(j) complete
   const uint32_t bar_w_full = bar_o + 16;         // [2] mailbox slot published
   const uint32_t bar_w_empty = bar_w_full + 16;   // [2] mailbox slot read by MMA thread + 8 softmax warps
-  const uint32_t tmem_slot = bar_w_empty + 16;
+  const uint32_t bar_qt = bar_w_empty + 16;       // [1] one-tile units: Q copied to TMEM by warpgroup 1 (128 arrivals)
+  const uint32_t tmem_slot = bar_qt + 16;
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_al + Cfg::OFF_BAR + Cfg::NUM_BARS * 8);
   uint8_t* mbox = smem_al + Cfg::OFF_MBOX;        // [2][32 B]
 
@@ -171,6 +176,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
       mbar_init(bar_q + 8 * t, 1); mbar_init(bar_q_empty + 8 * t, 1);
       mbar_init(bar_s + 8 * t, 1); mbar_init(bar_p + 8 * t, 128); mbar_init(bar_o + 8 * t, 1);
       mbar_init(bar_w_full + 8 * t, 1); mbar_init(bar_w_empty + 8 * t, 9);
+      mbar_init(bar_qt + 8 * t, 128);
     }
     for (int i = 0; i < NS; i++) { mbar_init(bar_kv_full + 8 * i, 1); mbar_init(bar_kv_empty + 8 * i, 1); }
     fence_barrier_init();
@@ -378,15 +384,17 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
           for (int ks = 0; ks < D / 16; ks++) {
             if (ks >= nks) break;                       // d = 96 / 32 stop early
             const uint32_t off = (ks >> 2) * (Cfg::SUB_BYTES >> 4) + (ks & 3) * 2;
-            umma_ss(tmem + Cfg::TM_S + t * 128, DESC_KMAJOR | (qa + off), DESC_KMAJOR | (kb + off), idesc_qk, ks > 0);
+            if constexpr (Cfg::TILES == 1) umma_ts(tmem + Cfg::TM_S, tmem + Cfg::TM_Q + ks * 8, DESC_KMAJOR | (kb + off), idesc_qk, ks > 0);
+            else umma_ss(tmem + Cfg::TM_S + t * 128, DESC_KMAJOR | (qa + off), DESC_KMAJOR | (kb + off), idesc_qk, ks > 0);
           }
           TC5_TRACE(2, trace_it + j - 1 - j_begin, t * 8 + 5);
           umma_commit(bar_s + 8 * t);
           if (release) umma_commit(bar_kv_empty + 8 * slot);
           if (j + 1 == (t == 0 ? tr0.je : tr1.je)) umma_commit(bar_q_empty + 8 * t);   // Q_t may be overwritten
         };
-        mbar_wait(bar_q, wi & 1);
+        mbar_wait(Cfg::TILES == 1 ? bar_qt : bar_q, wi & 1);
         mbar_wait(bar_q + 8, wi & 1);
+        if constexpr (Cfg::TILES == 1) tc_fence_after();
         if (!act0) mbar_arrive(bar_q_empty);
         if (!act1) mbar_arrive(bar_q_empty + 8);
         if (j_begin < j_end) {

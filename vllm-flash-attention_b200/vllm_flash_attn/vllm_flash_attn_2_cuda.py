@@ -113,6 +113,21 @@ class _on_device:
             self.g.__exit__(*a)
 
 
+_placeholder_cache = {}
+
+
+def _placeholders(dtype, device):
+    """The `p` (empty: no dropout, so no returned probabilities) and `rng_state` outputs of fwd / varlen_fwd
+    (flash_api.cpp:384-392,409).  Nothing ever writes them, so one pair per (dtype, device) is shared by
+    all calls instead of two allocator round trips per call."""
+    key = (dtype, device)
+    t = _placeholder_cache.get(key)
+    if t is None:
+        t = (torch.empty((0,), dtype=dtype, device=device), torch.zeros((2,), dtype=torch.int64, device=device))
+        _placeholder_cache[key] = t
+    return t
+
+
 def _pad_head(x, d_pad):
     return torch.nn.functional.pad(x, (0, d_pad - x.shape[-1])) if x.shape[-1] != d_pad else x
 
@@ -165,8 +180,7 @@ def fwd(q, k, v, out_, alibi_slopes_, p_dropout, softmax_scale, is_causal, windo
         if out_ is not None:
             out_.copy_(out)
             out = out_
-    p = torch.empty((0,), dtype=q.dtype, device=q.device)           # return_softmax needs dropout (off)
-    rng_state = torch.empty((2,), dtype=torch.int64, device=q.device)
+    p, rng_state = _placeholders(q.dtype, q.device)                 # return_softmax needs dropout (off)
     return [out, q_p, k_p, v_p, out_padded, lse, p, rng_state]
 
 
@@ -251,8 +265,7 @@ def varlen_fwd(q, k, v, out_, cu_seqlens_q, cu_seqlens_k, seqused_k, block_table
         if out_ is not None:
             out_.copy_(out)
             out = out_
-    p = torch.empty((0,), dtype=q.dtype, device=dev)
-    rng_state = torch.empty((2,), dtype=torch.int64, device=dev)
+    p, rng_state = _placeholders(q.dtype, dev)
     return [out, q_p, k_p, v_p, out_padded, lse, p, rng_state]
 
 
