@@ -62,9 +62,11 @@ template <int D> struct Tc5Cfg {
   // Q + one K + one V tile (64 KB each) fill shared memory and the K/V ring is 2 slots deep.
   static constexpr int TILES = D > 128 ? 1 : 2;
   static constexpr int UNIT_ROWS = TILES * 128;
-  static constexpr int NS = D == 256 ? 2 : (D == 128 ? 4 : 8);
+  // one-tile units: Q is only staged in shared memory on its way to TMEM, so it travels through the K/V ring
+  // as one more item (order per unit: Q, K_jb, V_jb, K_jb+1, ...) and the ring is 3 slots of 64 KB
+  static constexpr int NS = D == 256 ? 3 : (D == 128 ? 4 : 8);
   static constexpr int OFF_Q = 0;
-  static constexpr int OFF_KV = TILES * TILE_BYTES;
+  static constexpr int OFF_KV = TILES == 1 ? 0 : 2 * TILE_BYTES;
   static constexpr int OFF_BAR = OFF_KV + NS * TILE_BYTES;
   static constexpr int NUM_BARS = 4 /*q full,empty*/ + 2 * NS + 2 /*s*/ + 2 /*p*/ + 2 /*o*/ + 4 /*mailbox full,empty*/ + 2 /*q in TMEM (+pad)*/;
   static constexpr int OFF_MBOX = OFF_BAR + NUM_BARS * 8 + 16;      // after the TMEM base slot; 2 x 32 B
@@ -250,6 +252,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
       const int j_end = act0 || act1 ? max(tr0.je, tr1.je) : j_begin;
       if (lane == 0) {
         for (int t = 0; t < 2; t++) {
+          if (Cfg::TILES == 1 && t == 0) continue;              // one-tile units: Q_0 is a ring item (below)
           // both Q barriers flip once per work unit (inactive tile: plain arrive), so their parity is the unit's
           mbar_wait(bar_q_empty + 8 * t, (unit_idx & 1) ^ 1);   // the previous unit's last QK_t has read Q_t
           if (!(t == 0 ? act0 : act1)) { mbar_arrive(bar_q + 8 * t); continue; }
@@ -260,6 +263,20 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
         }
       }
       __syncwarp();
+      if constexpr (Cfg::TILES == 1) {
+        if (act0) {     // Q of this unit: next ring slot; warpgroup 1 moves it to TMEM, the issuer releases the slot
+          const int slot = ring % NS, round = ring / NS;
+          if (lane == 0) {
+            mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
+            mbar_expect_tx(bar_kv_full + 8 * slot, Cfg::TILE_BYTES);
+            for (int c = 0; c < ND; c++)
+              tma_load_4d(kv_sm + slot * Cfg::TILE_BYTES + c * Cfg::SUB_BYTES, &maps.q, bar_kv_full + 8 * slot,
+                          c * 64, wk.head, wk.q_row0 + m0, p.cu_seqlens_q ? 0 : wk.bidb);
+          }
+          ring++;
+        }
+        __syncwarp();
+      }
       if constexpr (!PAGED) {
         if (lane == 0) {
           for (int j = j_begin; j < j_end; j++) {
@@ -394,7 +411,10 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
         };
         mbar_wait(Cfg::TILES == 1 ? bar_qt : bar_q, wi & 1);
         mbar_wait(bar_q + 8, wi & 1);
-        if constexpr (Cfg::TILES == 1) tc_fence_after();
+        if constexpr (Cfg::TILES == 1) {
+          tc_fence_after();
+          if (act0) { mbar_arrive(bar_kv_empty + 8 * (ring % NS)); ring++; }   // Q is in TMEM: its ring slot is free
+        }
         if (!act0) mbar_arrive(bar_q_empty);
         if (!act1) mbar_arrive(bar_q_empty + 8);
         if (j_begin < j_end) {
