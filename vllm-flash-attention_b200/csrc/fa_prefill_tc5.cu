@@ -22,7 +22,8 @@
 // S0(j+1) the tensor core runs PV1(j) and QK1(j+1).
 // Head dims: instantiations D = 64 / 128 / 256 serve d = 32,64 / 96,128 / 160..256 (d is a run-time value:
 // TMA boxes clip at the true width, QK^T takes d/16 k-steps, PV has N = d).  D = 256 runs ONE Q tile per
-// work unit (O0 = [256,512), warpgroup 1 idle, 2-slot K/V ring of 64 KB tiles) — see Tc5Cfg::TILES.
+// work unit (TMEM: S [0,128) Q [128,256) O [256,512); warpgroup 1 copies Q to TMEM; Q, K, V share a 3-slot ring of
+// 64 KB tiles) — see Tc5Cfg::TILES.
 #include "fa_common.cuh"
 #include "fa_sm100.cuh"
 #include <algorithm>
@@ -58,8 +59,8 @@ template <int D> struct Tc5Cfg {
   static constexpr int SUB_BYTES = 128 * 128;               // 128 rows x 128 B
   static constexpr int TILE_BYTES = ND * SUB_BYTES;         // a Q / K / V tile
   // Q tiles per work unit.  d <= 128: two 128-row tiles ping-pong through the tensor core.  128 < d <= 256
-  // (D = 256): O alone takes 256 TMEM columns, so a unit is ONE 128-row tile (softmax warpgroup 1 stays idle),
-  // Q + one K + one V tile (64 KB each) fill shared memory and the K/V ring is 2 slots deep.
+  // (D = 256): O alone takes 256 TMEM columns, so a unit is ONE 128-row tile (softmax warpgroup 1 has no tile of
+  // its own: it moves Q into TMEM).
   static constexpr int TILES = D > 128 ? 1 : 2;
   static constexpr int UNIT_ROWS = TILES * 128;
   // one-tile units: Q is only staged in shared memory on its way to TMEM, so it travels through the K/V ring
