@@ -282,6 +282,11 @@ def test_varlen_empty_sequences_through_the_work_list():
     assert info["kernel_used"] == 1 and info["launches"] == 3     # schedule + prefill + decode
     info = _varlen_check([130, 0, 70], [130, 64, 0], h=4, hk=4, causal=False)
     assert info["kernel_used"] == 1
+    # one-tile units (d > 128): 128-row work units, Q through the K/V ring, empty rows / sequences in between
+    info = _varlen_check([600, 0, 1, 257, 0, 128, 300, 513, 40], [600, 50, 700, 257, 0, 0, 300, 513, 900], h=16, hk=4, d=256)
+    assert info["kernel_used"] == 1 and info["launches"] == 3
+    info = _varlen_check([130, 0, 70, 300], [130, 64, 0, 200], h=4, hk=2, d=192)
+    assert info["kernel_used"] == 1
 
 
 def test_varlen_many_sequences_mixed():

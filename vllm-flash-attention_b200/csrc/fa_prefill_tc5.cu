@@ -80,43 +80,6 @@ template <int D> struct Tc5Cfg {
   static constexpr int TM_Q = 128;
 };
 
-// exp2 of 32 scaled scores -> 16 packed bf16/fp16 pairs + row-sum accumulation.
-// The MUFU unit (16 ex2/clk/SM) needs exactly as many cycles per tile as the tensor pipe, so NEMU
-// of every 16 pairs are evaluated on the FMA pipe instead (FA4-style): 2^x = 2^n * 2^r with
-// n = round(x) taken from the magic-number add, r = x - n in [-0.5, 0.5], 2^r by a degree-3
-// minimax polynomial (max rel. error 7.6e-5, 26x below the bf16 rounding of P that follows), and
-// 2^n applied by adding n to the exponent field.  Everything but the exponent add is packed
-// fp32x2.  Inputs are clamped at -126 (result 2^-126 instead of 0), so callers use NEMU = 0 on
-// tiles that contain masked (-inf) scores.
-#ifndef FA_TC5_EMU
-#define FA_TC5_EMU 0
-#endif
-template <typename T, int NEMU>
-__device__ __forceinline__ void tc5_exp_chunk(const uint32_t (&s)[32], const float2 mul2, const float2 nms2,
-                                              float2& la, float2& lb, uint32_t (&pk)[16]) {
-#pragma unroll
-  for (int i = 0; i < 16; i++) {
-    // packed fp32x2: one FFMA2 scales and shifts two scores, one FADD2 accumulates two sums
-    float2 x = __ffma2_rn(make_float2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1])), mul2, nms2);
-    float2 pp;
-    if ((i & 1) && (i >> 1) < NEMU) {
-      x.x = fmaxf(x.x, -126.f); x.y = fmaxf(x.y, -126.f);
-      const float2 tt = __fadd2_rn(x, make_float2(12582912.f, 12582912.f));       // 1.5*2^23: low bits = round(x)
-      const float2 fl = __fadd2_rn(tt, make_float2(-12582912.f, -12582912.f));
-      const float2 r = __ffma2_rn(fl, make_float2(-1.f, -1.f), x);
-      float2 q = __ffma2_rn(r, make_float2(0.05520550534f, 0.05520550534f), make_float2(0.2426139712f, 0.2426139712f));
-      q = __ffma2_rn(q, r, make_float2(0.6932547688f, 0.6932547688f));
-      q = __ffma2_rn(q, r, make_float2(0.9999276996f, 0.9999276996f));
-      pp.x = __int_as_float(__float_as_int(q.x) + (__float_as_int(tt.x) << 23));
-      pp.y = __int_as_float(__float_as_int(q.y) + (__float_as_int(tt.y) << 23));
-    } else {
-      pp = make_float2(fast_exp2(x.x), fast_exp2(x.y));
-    }
-    if (i & 1) lb = __fadd2_rn(lb, pp); else la = __fadd2_rn(la, pp);
-    pk[i] = Pack2<T>::pack(pp.x, pp.y);
-  }
-}
-
 // Per-Q-tile KV tile range [jb, je) (in units of TC5_BN keys); empty when the tile has no rows
 // or no visible keys.
 struct TileRange { int jb, je; };
