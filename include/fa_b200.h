@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 3
+#define FA_B200_ABI_VERSION 4
 
 enum {
   FA_OK = 0,
@@ -162,10 +162,11 @@ int fa_b200_combine(const void* o_part, const float* lse_part, void* o, float* l
  * flash_fwd_kernel.h:1151-1221, lifted from splits to ranks).  Every rank pushes its packed fp32 record
  * [o (b,h,seqlen_q,d) | lse (b,h,seqlen_q)] into all ranks' receive areas through peer-mapped pointers
  * (NVLink stores), publishes a sequence number, waits for the peers' and LSE-combines.  recv[r] / flags[r]
- * are rank r's receive area ([2][world][record_elems] fp32) and flag array ([world] uint32, zeroed once)
- * as mapped into THIS process (e.g. torch symmetric memory buffer_ptrs); state is this rank's own
- * {calls, ctas_done} pair (zeroed once).  All ranks must make the same sequence of calls. */
+ * are rank r's receive area ([2][world][record_elems] fp32) and flag array ([world][FA_XCHG_CTAS] uint32,
+ * zeroed once) as mapped into THIS process (e.g. torch symmetric memory buffer_ptrs); state is this rank's own
+ * per-CTA call counters ([FA_XCHG_CTAS] uint32, zeroed once).  All ranks must make the same sequence of calls. */
 #define FA_MAX_PEERS 8
+#define FA_XCHG_CTAS 64
 typedef struct FaExchangeParams {
   void* recv[FA_MAX_PEERS];
   uint32_t* flags[FA_MAX_PEERS];

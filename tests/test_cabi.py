@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol():
 
 
 def test_params_layout_and_version():
-    assert lib.fa_b200_abi_version() == 3
+    assert lib.fa_b200_abi_version() == 4
     assert lib.fa_b200_params_size() == C.sizeof(FaFwdParams)
 
 

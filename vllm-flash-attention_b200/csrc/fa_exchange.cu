@@ -6,18 +6,19 @@
 // (reference src/flash_fwd_kernel.h:1151-1221) lifted from splits to ranks.
 //
 // Memory (all in a symmetric allocation, same layout on every rank; see vllm_flash_attn/sharded.py):
-//   recv[2][world][record]   receive area, double-buffered by call parity
-//   flags[world]             flags[r] = sequence number of the last record rank r has delivered here
-//   state[2]                 {calls completed, CTAs done pushing in the current call}
-// Protocol of call number n (n = state[0] + 1, read by every CTA before it pushes anything):
-//   1. every CTA copies its slice of the local record to recv[n&1][rank] of every rank (incl. self),
-//      fences system-wide and bumps state[1]; the CTA that completes the count resets it, sets
-//      state[0] = n and stores n into flags[rank] of every peer;
-//   2. every CTA waits until flags[r] >= n for all r, then merges its rows from recv[n&1][*].
-// A rank cannot run two calls ahead of a peer (its call n+1 needs the peer's flag n+1, sent only
-// after the peer finished call n), so two receive buffers suffice.  All state lives in device memory:
-// the launch is CUDA-graph replayable.  The wait is bounded (trap after ~4 s) so that a missing peer
-// surfaces as a launch failure, not a hung GPU.
+//   recv[2][world][record]        receive area, double-buffered by call parity
+//   flags[world][FA_XCHG_CTAS]    flags[r][c] = sequence number of the last slice CTA c of rank r delivered here
+//   state[FA_XCHG_CTAS]           state[c] = calls CTA c of this rank has completed
+// The rows of the record are dealt to the CTAs the same way on every rank, and CTA c both pushes and merges
+// exactly its own rows, so it depends on the peers' CTA c only.  Protocol of CTA c, call n = state[c] + 1:
+//   1. copy its rows (O row + lse) of the local record to recv[n&1][rank] of every rank (incl. self), fence
+//      system-wide, store n into flags[rank][c] of every rank;
+//   2. wait until flags[r][c] >= n for all r (one polling thread per peer), merge its rows from recv[n&1][*].
+// No count over the CTAs of a rank, no second fence, no CTA waits for data it does not merge.  A rank cannot
+// run two calls ahead of a peer (its call n+1 needs the peer's flag n+1, sent only after the peer finished
+// call n), so two receive buffers suffice.  All state lives in device memory: the launch is CUDA-graph
+// replayable.  The wait is bounded (trap after ~4 s) so that a missing peer surfaces as a launch failure,
+// not a hung GPU.
 #include "fa_common.cuh"
 #include "fa_launch.h"
 
@@ -47,47 +48,45 @@ __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
 
 __global__ void __launch_bounds__(256) fa_exchange_combine_kernel(const __grid_constant__ ExchangeParams p) {
   __shared__ unsigned s_n;
-  if (threadIdx.x == 0) s_n = ld_acquire_sys(p.state) + 1u;   // read before this CTA pushes: the count cannot complete yet
+  const int cta = blockIdx.x;
+  if (threadIdx.x == 0) s_n = p.state[cta] + 1u;               // only this CTA ever writes state[cta]
   __syncthreads();
   const unsigned n = s_n;
   const int64_t rows = (int64_t)p.b * p.h * p.sq;
-  const int64_t used = rows * (p.d + 1);                      // fp32 elements actually carried
-  const int64_t vec = (used + 3) / 4;                         // 16-byte pieces (record is padded to 16 B)
   const int64_t slot = ((int64_t)(n & 1u) * p.world + p.rank) * p.record;
+  const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
 
-  // ---- 1. push ----
-  const float4* src = reinterpret_cast<const float4*>(p.local);
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < vec; i += (int64_t)gridDim.x * blockDim.x) {
-    const float4 v = src[i];
-    for (int r = 0; r < p.world; r++) reinterpret_cast<float4*>(p.recv[r] + slot)[i] = v;
+  // ---- 1. push this CTA's rows: one warp per row, 16-byte pieces ----
+  for (int64_t row = (int64_t)cta * warps + (threadIdx.x >> 5); row < rows; row += (int64_t)gridDim.x * warps) {
+    for (int c = lane * 4; c < p.d; c += 128) {
+      const float4 v = *reinterpret_cast<const float4*>(p.local + row * p.d + c);
+      for (int r = 0; r < p.world; r++) *reinterpret_cast<float4*>(p.recv[r] + slot + row * p.d + c) = v;
+    }
+    if (lane == 0) {
+      const float l = p.local[rows * p.d + row];
+      for (int r = 0; r < p.world; r++) p.recv[r][slot + rows * p.d + row] = l;
+    }
   }
   __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) {
-    const unsigned done = atomicAdd(p.state + 1, 1u);
-    if (done == gridDim.x - 1) {                              // all CTAs of this rank have pushed and fenced
-      p.state[1] = 0u;
-      __threadfence_system();
-      for (int r = 0; r < p.world; r++) st_release_sys(p.flags[r] + p.rank, n);
-      st_release_sys(p.state, n);
-    }
-    // ---- 2. wait for every rank's record of call n ----
+  if (threadIdx.x < p.world) {
+    const int r = threadIdx.x;
+    st_release_sys(p.flags[r] + p.rank * FA_XCHG_CTAS + cta, n);
+    // ---- 2. wait for rank r's slice of call n ----
     long long t0;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    for (int r = 0; r < p.world; r++) {
-      while ((int)(ld_acquire_sys(p.flags[p.rank] + r) - n) < 0) {
-        long long t1;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-        if (t1 - t0 > 4000000000ll) __trap();
-      }
+    while ((int)(ld_acquire_sys(p.flags[p.rank] + r * FA_XCHG_CTAS + cta) - n) < 0) {
+      long long t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 4000000000ll) __trap();
     }
   }
+  if (threadIdx.x == 0) p.state[cta] = n;
   __syncthreads();
 
   // ---- 3. merge: one warp per row ----
   const float* base = p.recv[p.rank] + (int64_t)(n & 1u) * p.world * p.record;
-  const int lane = threadIdx.x & 31, warps = blockDim.x >> 5;
-  for (int64_t row = (int64_t)blockIdx.x * warps + (threadIdx.x >> 5); row < rows; row += (int64_t)gridDim.x * warps) {
+  for (int64_t row = (int64_t)cta * warps + (threadIdx.x >> 5); row < rows; row += (int64_t)gridDim.x * warps) {
     float ls[FA_MAX_PEERS], mx = -INFINITY;
 #pragma unroll
     for (int r = 0; r < FA_MAX_PEERS; r++) {
@@ -141,7 +140,7 @@ cudaError_t launch_exchange_combine(const FaExchangeParams& a, cudaStream_t stre
   const int64_t rows = (int64_t)a.b * a.h * a.seqlen_q;
   // every CTA has to be resident while it waits for the peers: keep the grid far below one wave
   int grid = (int)((rows + 7) / 8);
-  if (grid > 64) grid = 64;
+  if (grid > FA_XCHG_CTAS) grid = FA_XCHG_CTAS;
   if (grid < 1) grid = 1;
   fa_exchange_combine_kernel<<<grid, 256, 0, stream>>>(p);
   return cudaGetLastError();

@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("FA_B200_LIB", os.path.join(_HERE, "libfa_b200.so"))
 
 FA_OK = 0
 FA_ERR_WORKSPACE = -4
-ABI_VERSION = 3
+ABI_VERSION = 4
 FA_KERNEL_NONE, FA_KERNEL_TC5_PREFILL, FA_KERNEL_TILE, FA_KERNEL_DECODE = 0, 1, 2, 3
 OP_FWD, OP_VARLEN, OP_KVCACHE = 0, 1, 2
 

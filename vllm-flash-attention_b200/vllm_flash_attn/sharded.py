@@ -101,9 +101,12 @@ def merge_partials(records: torch.Tensor, b: int, h: int, sq: int, d: int, out_d
 
 
 # --------------------------------------------------------------------------------------------
+_XCHG_CTAS = 64            # FA_XCHG_CTAS (include/fa_b200.h)
+
+
 class PeerExchange:
     """Peer-memory state for the fused cross-GPU merge (fa_b200_exchange_combine): one symmetric
-    allocation per rank — receive area [2][world][record], flag array [world], state [2], and the local
+    allocation per rank — receive area [2][world][record], flag array [world][64], state [64], and the local
     staging record the decode kernel writes — mapped into every process of the box by torch symmetric
     memory (NVLink P2P).  Create it once (collectively, all ranks of `group`) for the largest
     (b, h, seqlen_q, d) that will be merged; `merge()` then costs one kernel launch per decode step and
@@ -120,8 +123,8 @@ class PeerExchange:
         self.record = (max_record_elems + 3) // 4 * 4
         recv_elems = 2 * self.world * self.record
         self.off_flags = recv_elems                       # fp32/uint32 element offsets inside the allocation
-        self.off_state = self.off_flags + 16
-        self.off_local = self.off_state + 16
+        self.off_state = self.off_flags + 8 * _XCHG_CTAS  # flags [FA_MAX_PEERS][FA_XCHG_CTAS]
+        self.off_local = self.off_state + _XCHG_CTAS      # state [FA_XCHG_CTAS]
         total = self.off_local + self.record
         if single:                                        # one rank: an ordinary allocation, same protocol
             self.buf = torch.zeros(total, dtype=torch.float32, device=device)
