@@ -22,8 +22,8 @@
 // S0(j+1) the tensor core runs PV1(j) and QK1(j+1).
 // Head dims: instantiations D = 64 / 128 / 256 serve d = 32,64 / 96,128 / 160..256 (d is a run-time value:
 // TMA boxes clip at the true width, QK^T takes d/16 k-steps, PV has N = d).  D = 256 runs ONE Q tile per
-// work unit (TMEM: S [0,128) Q [128,256) O [256,512); warpgroup 1 copies Q to TMEM; Q, K, V share a 3-slot ring of
-// 64 KB tiles) — see Tc5Cfg::TILES.
+// work unit (TMEM: S [0,128) Q [128,256) O [256,512); two softmax threads per row, fa_prefill_tc5_softmax_pair.inc;
+// Q, K, V share a 3-slot ring of 64 KB tiles) — see Tc5Cfg::TILES.
 #include "fa_common.cuh"
 #include "fa_sm100.cuh"
 #include <algorithm>
@@ -59,8 +59,8 @@ template <int D> struct Tc5Cfg {
   static constexpr int SUB_BYTES = 128 * 128;               // 128 rows x 128 B
   static constexpr int TILE_BYTES = ND * SUB_BYTES;         // a Q / K / V tile
   // Q tiles per work unit.  d <= 128: two 128-row tiles ping-pong through the tensor core.  128 < d <= 256
-  // (D = 256): O alone takes 256 TMEM columns, so a unit is ONE 128-row tile (softmax warpgroup 1 has no tile of
-  // its own: it moves Q into TMEM).
+  // (D = 256): O alone takes 256 TMEM columns, so a unit is ONE 128-row tile that both softmax warpgroups
+  // share (two threads per row).
   static constexpr int TILES = D > 128 ? 1 : 2;
   static constexpr int UNIT_ROWS = TILES * 128;
   // one-tile units: Q is only staged in shared memory on its way to TMEM, so it travels through the K/V ring
@@ -71,8 +71,10 @@ template <int D> struct Tc5Cfg {
   static constexpr int OFF_BAR = OFF_KV + NS * TILE_BYTES;
   static constexpr int NUM_BARS = 4 /*q full,empty*/ + 2 * NS + 2 /*s*/ + 2 /*p*/ + 2 /*o*/ + 4 /*mailbox full,empty*/ + 2 /*q in TMEM (+pad)*/;
   static constexpr int OFF_MBOX = OFF_BAR + NUM_BARS * 8 + 16;      // after the TMEM base slot; 2 x 32 B
-  static constexpr int OFF_STAGE = (OFF_MBOX + 64 + 1023) / 1024 * 1024;   // epilogue staging: 4 KB per active softmax warp, TMA-store sources (1024 B aligned)
-  static constexpr int SMEM = OFF_STAGE + 4 * TILES * 4096 + 1024;  // +1024: manual alignment
+  static constexpr int OFF_XCHG = OFF_MBOX + 64;                    // one-tile units: row max / row sum swap area of the warp pairs (2 x 128 floats) + 16 flags
+  static constexpr int OFF_STAGE = (OFF_XCHG + (TILES == 1 ? 1024 + 64 : 0) + 1023) / 1024 * 1024;   // epilogue staging: 4 KB per softmax warp, TMA-store sources (1024 B aligned)
+  static constexpr int SMEM = OFF_STAGE + 8 * 4096 + 1024;          // +1024: manual alignment
+  static_assert(SMEM <= 232448, "shared memory budget");
   static constexpr int TM_S = 0, TM_O = 256;                // TMEM column bases; tile t adds t*128
   // One-tile units (D = 256): the S1 region holds Q as a TMEM A operand (column x = elements 2x, 2x+1 of the
   // row).  QK^T from shared memory needs the full 128 B/clk of shared-memory bandwidth (4 KB of Q + 4 KB of K
@@ -127,7 +129,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
   const uint32_t bar_o = bar_p + 16;              // [2] PV_t(j) complete
   const uint32_t bar_w_full = bar_o + 16;         // [2] mailbox slot published
   const uint32_t bar_w_empty = bar_w_full + 16;   // [2] mailbox slot read by MMA thread + 8 softmax warps
-  const uint32_t bar_qt = bar_w_empty + 16;       // [1] one-tile units: Q copied to TMEM by warpgroup 1 (128 arrivals)
+  const uint32_t bar_qt = bar_w_empty + 16;       // [1] one-tile units: Q copied to TMEM by the softmax warps (256 arrivals)
   const uint32_t tmem_slot = bar_qt + 16;
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_al + Cfg::OFF_BAR + Cfg::NUM_BARS * 8);
   uint8_t* mbox = smem_al + Cfg::OFF_MBOX;        // [2][32 B]
@@ -140,11 +142,13 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
     prefetch_tmap(&maps.q); prefetch_tmap(&maps.k); prefetch_tmap(&maps.v); prefetch_tmap(&maps.o);
     for (int t = 0; t < 2; t++) {
       mbar_init(bar_q + 8 * t, 1); mbar_init(bar_q_empty + 8 * t, 1);
-      mbar_init(bar_s + 8 * t, 1); mbar_init(bar_p + 8 * t, 128); mbar_init(bar_o + 8 * t, 1);
+      mbar_init(bar_s + 8 * t, 1); mbar_init(bar_p + 8 * t, 128 * (3 - Cfg::TILES)); mbar_init(bar_o + 8 * t, 1);   // one-tile units: both warpgroups publish P_0
       mbar_init(bar_w_full + 8 * t, 1); mbar_init(bar_w_empty + 8 * t, 9);
-      mbar_init(bar_qt + 8 * t, 128);
+      mbar_init(bar_qt + 8 * t, 256);
     }
     for (int i = 0; i < NS; i++) { mbar_init(bar_kv_full + 8 * i, 1); mbar_init(bar_kv_empty + 8 * i, 1); }
+    if constexpr (Cfg::TILES == 1)      // "check failed" tags of the warp pairs: 0 matches no iteration
+      for (int i = 0; i < 16; i++) reinterpret_cast<volatile int*>(smem_al + Cfg::OFF_XCHG + 1024)[i] = 0;
     fence_barrier_init();
   }
   if (warp == TC5_MMA_WARP) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
@@ -435,7 +439,11 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
   } else if (warp < 8) {
     setmaxnreg_inc<TC5_REGS_SOFTMAX>();
     // =============================== softmax warpgroups ===============================
+    if constexpr (Cfg::TILES == 1) {
+#include "fa_prefill_tc5_softmax_pair.inc"
+    } else {
 #include "fa_prefill_tc5_softmax.inc"
+    }
   } else {
     setmaxnreg_dec<TC5_REGS_OTHER>();
   }
