@@ -193,7 +193,26 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def _ensure_built():
+    """Build outputs are git-ignored: a fresh checkout compiles the library in-tree (rank 0 only) before importing it."""
+    pkg = os.path.join(ROOT, "vllm-flash-attention_b200")
+    so = os.path.join(pkg, "vllm_flash_attn", "libfa_b200.so")
+    if os.path.exists(so):
+        return
+    if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+        subprocess.run(["bash", os.path.join(pkg, "build.sh")], check=True, stdout=subprocess.DEVNULL)
+    else:
+        last = -1
+        for _ in range(600):            # wait until rank 0 has finished linking (size stable)
+            size = os.path.getsize(so) if os.path.exists(so) else -1
+            if size > 0 and size == last:
+                break
+            last = size
+            time.sleep(2)
+
+
 def run_ours(args):
+    _ensure_built()
     import torch
     import torch.distributed as dist
     import vllm_flash_attn as fa
