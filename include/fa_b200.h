@@ -83,7 +83,8 @@ typedef struct FaFwdParams {
   int64_t block_table_batch_stride;
   int32_t page_block_size;
   int32_t max_blocks_per_seq;
-  int32_t num_blocks;          /* size of the page pool (bounds check / tensor maps) */
+  int32_t num_blocks;          /* size of the page pool; fwd_kvcache without block_table: batch entries of the cache
+                                  (bounds / tensor maps; 0 = unknown, the prefill-sized call then runs on the tile kernel) */
   const int32_t* cache_batch_idx; /* (b) or NULL */
   int64_t total_q, total_k;    /* varlen: rows in q / k (tensor-map bounds) */
 

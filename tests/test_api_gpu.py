@@ -44,7 +44,7 @@ def test_auto_dispatch_picks_expected_kernels():
     kc3 = torch.randn(3, 400, 4, 160, device=dev, dtype=dt)
     fa.flash_attn_with_kvcache(q3, kc3, kc3, cache_seqlens=torch.tensor([300], dtype=torch.int32, device=dev),
                                cache_batch_idx=torch.tensor([2], dtype=torch.int32, device=dev))
-    assert _ext().last_call_info["kernel_used"] == 2          # tile kernel (cache_batch_idx with many query rows)
+    assert _ext().last_call_info["kernel_used"] == 1          # non-paged cache as one page per sequence (cache_batch_idx = its block table)
     q4 = torch.randn(2, 1, 8, 192, device=dev, dtype=dt); k4 = torch.randn(2, 300, 2, 192, device=dev, dtype=dt)
     fa.flash_attn_with_kvcache(q4, k4, k4)
     assert _ext().last_call_info["kernel_used"] == 3          # decode, every head dim of the reference build
@@ -394,3 +394,36 @@ def test_varlen_seqused_k():
     pt, _ = orc.attention_ref_varlen(q, kc, vc, cu_q, cu_u, causal=True, upcast=False, reorder_ops=True)
     err, err_pt = (out.float() - ref32.float()).abs().max().item(), (pt.float() - ref32.float()).abs().max().item()
     assert err <= 2 * err_pt + 1e-5, (err, err_pt)
+
+
+@pytest.mark.parametrize("d,use_idx,s_cache", [(128, False, 700), (128, True, 300), (64, True, 100), (256, False, 513), (96, True, 40)])
+def test_kvcache_prefill_over_a_non_paged_cache(d, use_idx, s_cache):
+    """flash_attn_with_kvcache with many query rows against a NON-paged cache addressed through cache_seqlens and
+    cache_batch_idx (tests/test_flash_attn.py:1816-2076): runs on the tcgen05 kernel with the cache seen as one page per
+    sequence.  Rows past cache_seqlens hold NaN: they must never reach the output."""
+    import vllm_flash_attn as fa
+    torch.manual_seed(2)
+    dev, dt, b, h, hk = "cuda", torch.bfloat16, 3, 8, 2
+    b_c = 7 if use_idx else b
+    lens = torch.tensor([s_cache, max(s_cache // 2, 1), max(s_cache - 17, 1)], dtype=torch.int32, device=dev)
+    sq = min(60, s_cache // 2) if s_cache < 128 else 200
+    lens = torch.maximum(lens, torch.tensor(sq, dtype=torch.int32, device=dev))
+    kc = torch.randn(b_c, s_cache, hk, d, device=dev, dtype=dt); vc = torch.randn_like(kc)
+    idx = torch.tensor([5, 0, 3], dtype=torch.int32, device=dev) if use_idx else None
+    sel = idx.long() if use_idx else torch.arange(b, device=dev)
+    dead = torch.arange(s_cache, device=dev).view(1, -1) >= lens.view(-1, 1).long()          # (b, s_cache)
+    kc[sel] = torch.where(dead.view(b, s_cache, 1, 1), torch.full_like(kc[sel], float("nan")), kc[sel])
+    vc[sel] = torch.where(dead.view(b, s_cache, 1, 1), torch.full_like(vc[sel], float("nan")), vc[sel])
+    q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
+    out, lse = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=lens, cache_batch_idx=idx, causal=True, return_softmax_lse=True)
+    assert _ext().last_call_info["kernel_used"] == 1
+    kpm = ~dead
+    kg, vg = torch.nan_to_num(kc[sel]), torch.nan_to_num(vc[sel])
+    ref32, _ = orc.attention_ref(q, kg, vg, None, kpm, causal=True)
+    pt, _ = orc.attention_ref(q, kg, vg, None, kpm, causal=True, upcast=False, reorder_ops=True)
+    assert not torch.isnan(out.float()).any()
+    err, err_pt = (out.float() - ref32.float()).abs().max().item(), (pt.float() - ref32.float()).abs().max().item()
+    assert err <= 3 * err_pt + 1e-5, (err, err_pt)
+    lref = orc.lse_ref(q, kg, kpm, None, None, causal=True)
+    fin = torch.isfinite(lref)
+    assert (lse[fin] - lref[fin]).abs().max().item() < 2e-3

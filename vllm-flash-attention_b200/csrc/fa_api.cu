@@ -59,6 +59,23 @@ static int device_sms() {
 
 enum Op { OP_FWD = 0, OP_VARLEN = 1, OP_KVCACHE = 2 };
 
+// fwd_kvcache over a NON-paged cache with per-sequence lengths and / or cache_batch_idx (flash_api.cpp:859-901) on the
+// tcgen05 prefill kernel: the cache is a page pool whose pages are whole cache entries (seqlen_k rows, one page per
+// sequence, so no tile straddles a page) and cache_batch_idx is its one-column block table; the paged path's V-tail fill
+// keeps rows past cache_seqlens (which may hold anything) out of P.V.  Rewrites *k on success.
+static bool as_single_page(const FaFwdParams* a, int op, KParams* k) {
+  if (op != OP_KVCACHE || a->block_table || a->num_blocks <= 0 || a->seqlen_k <= 0) return false;
+  if (!a->cache_batch_idx && !(a->cu_seqlens_k && !k->is_seqlens_k_cumulative)) return false;
+  KParams t = *k;
+  t.single_page = 1;
+  t.block_table = a->cache_batch_idx; t.block_table_batch_stride = 1;
+  t.page_block_size = a->seqlen_k; t.max_blocks_per_seq = 1; t.num_blocks = a->num_blocks;
+  t.cache_batch_idx = nullptr;
+  if (!tc5_supported(t)) return false;
+  *k = t;
+  return true;
+}
+
 struct Plan {
   KParams k;
   int kernel;      // FA_KERNEL_*
@@ -152,7 +169,7 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   pl->decode_rows = 0;
   if (kernel == FA_KERNEL_NONE) {
     if (decode_supported(a->d, rows)) kernel = FA_KERNEL_DECODE;
-    else if (!k.partial && tc5_supported(k)) {
+    else if (!k.partial && (tc5_supported(k) || as_single_page(a, op, &k))) {
       kernel = FA_KERNEL_TC5_PREFILL;
       // A varlen batch may mix prompts with single-token (or few-token) sequences — vLLM's chunked
       // prefill.  Those would waste a 256-row tile per head, so they are routed to the decode
@@ -161,7 +178,7 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
     } else kernel = FA_KERNEL_TILE;
   }
   if (kernel == FA_KERNEL_DECODE) FA_CHECK(decode_supported(a->d, rows), "decode kernel: d/rows not supported");
-  if (kernel == FA_KERNEL_TC5_PREFILL) FA_CHECK(!k.partial && tc5_supported(k), "tcgen05 prefill kernel: shape/layout not supported");
+  if (kernel == FA_KERNEL_TC5_PREFILL) FA_CHECK(!k.partial && (tc5_supported(k) || as_single_page(a, op, &k)), "tcgen05 prefill kernel: shape/layout not supported");
   if (kernel == FA_KERNEL_TILE) FA_CHECK(tile_supported(a->d), "head dimension must be a multiple of 32 (reference build: -DFLASHATTENTION_DISABLE_UNEVEN_K)");
   pl->kernel = kernel;
 

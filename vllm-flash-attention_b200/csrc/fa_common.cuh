@@ -38,6 +38,8 @@ struct KParams {
   int kv_shard_start, kv_shard_len;               // sequence-sharded decode: this rank holds keys [start, start+len) of every sequence (len 0 = off)
   int2* work_items; int* work_header;           // tcgen05 prefill: cost-sorted (sequence, m_block) list + {draw counter, count}; NULL = static order
   long long* trace;                             // FA_TC5_TRACE builds only: per-event clock64 stamps of one CTA
+  int single_page;                              // tcgen05 prefill over a NON-paged cache: each cache entry is one page of seqlen_k rows,
+                                                // block_table (if any) is cache_batch_idx with one column, else block = sequence index
   int partial;                                  // write fp32 partials (o_accum/lse_accum, -inf for empty rows) even with 1 split
 };
 

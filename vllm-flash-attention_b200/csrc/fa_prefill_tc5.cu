@@ -267,7 +267,8 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
         // contains the end of the sequence is special: rows >= seqlen_k hold whatever the pool holds
         // (possibly NaN) and 0 * NaN would poison P.V, so its boxes that reach past the end are copied
         // by hand (valid rows) / zero-filled (the rest) in the 128-B swizzle TMA would have used.
-        const int* table = p.block_table + (int64_t)wk.bidb * p.block_table_batch_stride;
+        // single_page without cache_batch_idx: no table, block = sequence index
+        const int* table = p.block_table ? p.block_table + (int64_t)wk.bidb * p.block_table_batch_stride : nullptr;
         for (int j = j_begin; j < j_end; j++) {
           const int row0 = j * TC5_BN;
           const int valid = min(TC5_BN, sk - row0);                    // rows of this tile inside the sequence (>= 1)
@@ -286,7 +287,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
                 uint4 val = make_uint4(0, 0, 0, 0);
                 if (r < valid && c * 64 + ch * 8 < p.d) {
                   const int g = row0 + r, pg = g / page;
-                  const int blk = table[min(pg, p.max_blocks_per_seq - 1)];
+                  const int blk = table ? table[min(pg, p.max_blocks_per_seq - 1)] : wk.bidb;
                   val = *reinterpret_cast<const uint4*>(vbase + (int64_t)blk * p.v_batch_stride +
                                                         (int64_t)(g - pg * page) * p.v_row_stride + c * 64 + ch * 8);
                 }
@@ -300,7 +301,7 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
             __syncwarp();
             if (lane < n_tma_boxes) {
               const int g = row0 + lane * box_rows, pg = g / page;
-              const int blk = table[min(pg, p.max_blocks_per_seq - 1)];
+              const int blk = table ? table[min(pg, p.max_blocks_per_seq - 1)] : wk.bidb;
               for (int c = 0; c < ND; c++)
                 tma_load_4d(dst + c * Cfg::SUB_BYTES + lane * box_rows * 128, kv == 0 ? &maps.k : &maps.v, bar,
                             c * 64, kvh, g - pg * page, blk);
@@ -548,7 +549,10 @@ bool tc5_supported(const KParams& p) {
   if (p.d < 32 || p.d > 256 || p.d % 32 != 0) return false;   // every head dim of the reference build
   if (p.cache_batch_idx) return false;
   if (p.num_splits > 1) return false;
-  if (p.block_table) {
+  if (p.single_page) {
+    // a non-paged cache seen as one page per sequence (fa_api.cu, as_single_page): no tile straddles a page
+    if (p.page_block_size <= 0 || p.num_blocks <= 0 || p.max_blocks_per_seq != 1 || p.cu_seqlens_q) return false;
+  } else if (p.block_table) {
     // paged K/V: a 128-key tile must be a whole number of pages, or a page a whole number of tiles
     const int pg = p.page_block_size;
     if (pg <= 0 || !(pg % TC5_BN == 0 || TC5_BN % pg == 0) || p.num_blocks <= 0) return false;
@@ -578,7 +582,7 @@ static cudaError_t launch_tc5_t(const KParams& p, const Tc5Maps& maps, int grid,
 template <typename T, int D>
 static cudaError_t launch_tc5_d(const KParams& p, const Tc5Maps& maps, int grid, cudaStream_t stream) {
   const bool alibi = p.alibi_slopes != nullptr;
-  if (p.block_table) return alibi ? launch_tc5_t<T, D, true, true>(p, maps, grid, stream) : launch_tc5_t<T, D, false, true>(p, maps, grid, stream);
+  if (p.block_table || p.single_page) return alibi ? launch_tc5_t<T, D, true, true>(p, maps, grid, stream) : launch_tc5_t<T, D, false, true>(p, maps, grid, stream);
   return alibi ? launch_tc5_t<T, D, true, false>(p, maps, grid, stream) : launch_tc5_t<T, D, false, false>(p, maps, grid, stream);
 }
 
@@ -622,7 +626,7 @@ cudaError_t launch_prefill_tc5(const KParams& p, bool is_bf16, int64_t total_q, 
   const int64_t q_rows = varlen ? total_q : p.seqlen_q;
   bool ok = make_map(&maps.q, p.q, is_bf16, TC5_BM, p.d, p.h, q_rows, varlen ? 1 : p.b, p.q_head_stride, p.q_row_stride, p.q_batch_stride) &&
             make_map(&maps.o, p.o, is_bf16, 32, p.d, p.h, q_rows, varlen ? 1 : p.b, p.o_head_stride, p.o_row_stride, p.o_batch_stride);
-  if (p.block_table) {   // (d, heads, row in page, block)
+  if (p.block_table || p.single_page) {   // (d, heads, row in page, block)
     const int box = p.page_block_size < TC5_BN ? p.page_block_size : TC5_BN;
     ok = ok && make_map(&maps.k, p.k, is_bf16, box, p.d, p.h_k, p.page_block_size, p.num_blocks, p.k_head_stride, p.k_row_stride, p.k_batch_stride) &&
          make_map(&maps.v, p.v, is_bf16, box, p.d, p.h_k, p.page_block_size, p.num_blocks, p.v_head_stride, p.v_row_stride, p.v_batch_stride);

@@ -356,6 +356,8 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
         if paged:
             P.block_table, P.block_table_batch_stride = block_table_.data_ptr(), block_table_.stride(0)
             P.page_block_size, P.max_blocks_per_seq, P.num_blocks = page, max_blocks, num_blocks
+        else:
+            P.num_blocks = b_c          # batch entries of the dense cache (extent of the K/V tensor maps)
         _alibi(P, alibi_slopes_, b, h, dev)
         P.num_splits = num_splits
 
