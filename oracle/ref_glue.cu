@@ -56,7 +56,7 @@ extern "C" const char* ref_fa2_last_error(void) { return g_err; }
 // Always reports the 128-split worst case so the caller need not know the heuristic.
 extern "C" size_t ref_fa2_workspace_bytes(const FaFwdParams* p) {
   size_t rows = (size_t)p->b * p->h * std::max(p->seqlen_q, 1);
-  return 128 * rows * (size_t)(round_up(p->d, 32) + 1) * sizeof(float);
+  return 128 * rows * (size_t)(round_up(p->d, 32) + 1) * sizeof(float) + 16;
 }
 
 // op: 0 = mha_fwd, 1 = mha_varlen_fwd, 2 = mha_fwd_kvcache.
@@ -142,10 +142,10 @@ extern "C" int ref_fa2_run(FaFwdParams* a, int op, void* stream_) {
     if (P.num_splits > 128) { snprintf(g_err, sizeof g_err, "num_splits > 128 not supported"); return FA_ERR_INVALID; }
     if (P.num_splits > 1) {
       size_t rows = (size_t)b * h * seqlen_q;
-      size_t need = (size_t)P.num_splits * rows * (P.d_rounded + 1) * sizeof(float);
+      size_t need = (size_t)P.num_splits * rows * (P.d_rounded + 1) * sizeof(float) + 16;
       if (!a->workspace || a->workspace_bytes < need) { snprintf(g_err, sizeof g_err, "workspace too small"); return FA_ERR_WORKSPACE; }
       P.softmax_lseaccum_ptr = a->workspace;
-      P.oaccum_ptr = (float*)a->workspace + (size_t)P.num_splits * rows;
+      P.oaccum_ptr = (float*)a->workspace + ((size_t)P.num_splits * rows + 3) / 4 * 4;   // the combine kernel reads 16-byte pieces
     }
   }
   a->num_splits = P.num_splits;
