@@ -271,7 +271,7 @@ def attention_ref_varlen(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, wind
                              upcast=upcast, reorder_ops=reorder_ops)
         out[q0:q1] = o[0]
         l_i = lse_ref(qi, ki, attn_bias=bias, causal=causal, window_size=window_size)[0]
-        if bias is not None and causal:
+        if bias is not None and causal and window_size[0] < 0:   # sliding-window causal is 'local' to the kernel: |i-j| form, no shift
             # kernel convention: causal ALiBi bias is slope*j (csrc/flash_attn/src/mask.h:181), the
             # test helper's is slope*(j-(sk-1)) (tests/test_flash_attn.py:38-39): same out, LSE
             # differs by the row-constant slope*(sk-1)

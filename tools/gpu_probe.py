@@ -148,7 +148,7 @@ def run_case(spec):
         ref32, _ = orc.attention_ref(q, k, v, attn_bias=bias, causal=causal, window_size=window)
         out_pt, _ = orc.attention_ref(q, k, v, attn_bias=bias, causal=causal, window_size=window, upcast=False, reorder_ops=True)
         lref = orc.lse_ref(q, k, attn_bias=bias, causal=causal, window_size=window)
-        if slopes is not None and causal:   # the kernel's causal ALiBi bias is slope*j (src/mask.h:181),
+        if slopes is not None and causal and window[0] < 0:   # the kernel's causal ALiBi bias is slope*j (src/mask.h:181),
             lref = lref + slopes.view(b, h, 1) * (sk - 1)   # the oracle's slope*(j-(sk-1)): constant row shift
         ork, lrk = _util.ref_kernel_fwd(q, k, v, causal, window, slopes) if refk else (None, None)
         res.update(errs(out, ref32, out_pt, ork))
@@ -247,7 +247,7 @@ def run_case(spec):
         out_pt, _ = orc.attention_ref(q, kfull, vfull, None, kpm, bias, causal=causal, window_size=window,
                                       upcast=False, reorder_ops=True)
         lref = orc.lse_ref(q, kfull, kpm, None, bias, causal=causal, window_size=window)
-        if slopes is not None and causal:
+        if slopes is not None and causal and window[0] < 0:
             lref = lref + slopes.view(b, h, 1) * (S - 1)
         ork = None
         if refk and slopes is None:
