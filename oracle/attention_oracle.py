@@ -261,7 +261,8 @@ def attention_ref_varlen(q, k, v, cu_seqlens_q, cu_seqlens_k, causal=False, wind
         if alibi_slopes is not None:
             sl = alibi_slopes if alibi_slopes.dim() == 2 else alibi_slopes.unsqueeze(0)
             sl = sl[i:i + 1] if sl.shape[0] > 1 else sl
-            bias = attn_bias_from_alibi_slopes(sl.float(), q1 - q0, k1 - k0, causal=causal)
+            # sliding-window causal is 'local' to the kernels (flash_api.cpp:119-126): ALiBi in its |i - j| form (mask.h:183)
+            bias = attn_bias_from_alibi_slopes(sl.float(), q1 - q0, k1 - k0, causal=causal and window_size[0] < 0)
         qi, ki, vi = q[q0:q1].unsqueeze(0), k[k0:k1].unsqueeze(0), v[k0:k1].unsqueeze(0)
         if k1 == k0:
             out[q0:q1] = 0

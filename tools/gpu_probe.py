@@ -144,7 +144,7 @@ def run_case(spec):
         if spec["grow"]:
             k = (k.float() * torch.linspace(0.2, 6.0, sk, device=dev).view(1, sk, 1, 1)).to(dt)
         out, lse, _ = fa.flash_attn_func(q, k, v, causal=causal, window_size=window, alibi_slopes=slopes, return_attn_probs=True)
-        bias = orc.attn_bias_from_alibi_slopes(slopes, sq, sk, causal=causal) if slopes is not None else None
+        bias = orc.attn_bias_from_alibi_slopes(slopes, sq, sk, causal=causal and window[0] < 0) if slopes is not None else None
         ref32, _ = orc.attention_ref(q, k, v, attn_bias=bias, causal=causal, window_size=window)
         out_pt, _ = orc.attention_ref(q, k, v, attn_bias=bias, causal=causal, window_size=window, upcast=False, reorder_ops=True)
         lref = orc.lse_ref(q, k, attn_bias=bias, causal=causal, window_size=window)
@@ -242,7 +242,7 @@ def run_case(spec):
         kpm = torch.arange(S, device=dev).expand(b, S) < lens_d.view(-1, 1)
         bias = None
         if slopes is not None:
-            bias = orc.attn_bias_from_alibi_slopes(slopes, sq, S, None, kpm, causal=causal)
+            bias = orc.attn_bias_from_alibi_slopes(slopes, sq, S, None, kpm, causal=causal and window[0] < 0)
         ref32, _ = orc.attention_ref(q, kfull, vfull, None, kpm, bias, causal=causal, window_size=window)
         out_pt, _ = orc.attention_ref(q, kfull, vfull, None, kpm, bias, causal=causal, window_size=window,
                                       upcast=False, reorder_ops=True)
