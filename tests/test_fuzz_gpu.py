@@ -1,0 +1,28 @@
+"""GPU: randomised parity sweep through the automatic kernel choice — random head dims (32..256), lengths, causal /
+sliding-window / ALiBi masks, page sizes, varlen batches with single-token sequences, split-KV — every case against
+the fp32 oracle with the reference's criterion (tests/test_flash_attn.py:1085-1087, :2075-2076).  The generator
+(tools/fuzz.py) stays inside the domain of the reference's own tests (window sizes below seqlen_k)."""
+import random
+
+import pytest
+
+import _util  # noqa: F401  (sys.path)
+from tools.fuzz import random_spec
+from tools.gpu_probe import run_case
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("seed", [11, 12, 13])
+def test_random_cases_match_the_oracle(seed):
+    rng = random.Random(seed)
+    kernels = set()
+    for i in range(60):
+        spec = random_spec(rng, seed * 100000 + i)
+        r = run_case(spec)
+        mult = 3 if spec["kind"] == "kvcache" else 2
+        assert not r["nan"], (spec, r)
+        assert r["err"] <= mult * r["err_pt"] + 1e-5, (spec, r)
+        assert r["lse_err"] < 2e-3, (spec, r)
+        kernels.add(r["kernel_used"])
+    assert {1, 3} <= kernels          # both fast kernels were exercised
