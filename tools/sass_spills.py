@@ -13,7 +13,7 @@ for ln in names.splitlines():
     if m:
         cur = m.group(1)
         continue
-    if cur and pat in cur and re.search(r"/\*[0-9a-f]{4}\*/", ln):
+    if cur and pat in cur and re.search(r"/\*[0-9a-f]{4,}\*/", ln):
         lines.append(ln)
 ins = []
 for ln in lines:

@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(384, 1) bench(float* out, long long* clk, floa
   const int t = warp >> 2, wq = warp & 3;
   const uint32_t tm_s = tmem + ((uint32_t)(wq * 32) << 16) + t * 128;
   // fill S with moderate scores
-  {
+  if (warp < 8) {
     uint32_t r[32];
 #pragma unroll
     for (int c = 0; c < 4; c++) {
@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(384, 1) bench(float* out, long long* clk, floa
   }
   const long long t1 = clock64();
   out[threadIdx.x] = l_sum + m_ref;
-  if (threadIdx.x == 0) clk[0] = t1 - t0;
+  if (threadIdx.x == 0 && blockIdx.x == 0) clk[0] = t1 - t0;
   mbar_arrive(smem_u32(&spin_bar));
   }
   tc_fence_before();
@@ -195,14 +195,15 @@ int main() {
   float* out; long long* clk;
   cudaMalloc(&out, 4096); cudaMalloc(&clk, 8);
   cudaFuncSetAttribute(bench<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-  for (int mma = 0; mma <= 1; mma++)
-  for (int spin = 0; spin <= 1; spin++) {
-    const int wps = 1;
-    if (mma && !spin) continue;
-    for (int rep = 0; rep < 2; rep++) bench<__nv_bfloat16><<<1, 128 * (wps + spin), 100 * 1024>>>(out, clk, 0.1275f, 0.f, 4 * wps, mma);
+  for (int grid : {1, 148})
+  for (int wps = 1; wps <= 2; wps++)
+  for (int mma = 0; mma <= 1; mma++) {
+    const int spin = 1;     // 12 warps as in the kernel: wps*4 working, the rest wait on an mbarrier (one of them issues MMAs)
+    for (int rep = 0; rep < 2; rep++) bench<__nv_bfloat16><<<grid, 384, 100 * 1024>>>(out, clk, 0.1275f, 0.f, 4 * wps, mma);
     long long h = 0; cudaMemcpy(&h, clk, 8, cudaMemcpyDeviceToHost);
-    printf("VARIANT %d  working warps/SMSP=%d spinning warps/SMSP=%d mma=%d  %.0f clk per tile (per warp), %.0f clk per tile per SMSP\n", VARIANT, wps, spin, mma,
+    printf("VARIANT %d grid=%d working warps/SMSP=%d mma=%d  %.0f clk per tile (per warp), %.0f clk per tile per SMSP\n", VARIANT, grid, wps, mma,
            (double)h / TILES, (double)h / TILES / wps);
+    (void)spin;
   }
   printf("status: %s\n", cudaGetErrorString(cudaDeviceSynchronize()));
   return 0;

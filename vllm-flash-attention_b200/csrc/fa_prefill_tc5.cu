@@ -49,6 +49,13 @@ constexpr int TC5_THREADS = 384;       // 3 warpgroups; warps 10-11 idle (setmax
 // one of warps 8-11, so 2*224 + 56 (= 3*168, the launch allocation) is the most the split can give.
 constexpr int TC5_REGS_SOFTMAX = 224, TC5_REGS_OTHER = 56;
 constexpr int TC5_PRODUCER_WARP = 8, TC5_MMA_WARP = 9;
+#ifndef FA_TC5_GOVERNOR
+#define FA_TC5_GOVERNOR 0
+#endif
+#ifndef FA_TC5_GOV_MARGIN
+#define FA_TC5_GOV_MARGIN 24
+#endif
+__device__ __forceinline__ uint32_t clock32() { uint32_t c; asm volatile("mov.u32 %0, %%clock;" : "=r"(c)); return c; }
 
 struct Tc5Maps { CUtensorMap q, k, v, o; };   // o: 64 x 1 x 32 x 1 box (one warp's epilogue slab)
 template <typename T> struct IsBf16 { static constexpr bool value = false; };
@@ -336,6 +343,14 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
     if (elect_one()) {
       int ring = 0;               // K/V ring cursor (same sequence of items as the producer's)
       int pbits = 0;              // bit t: parity of the softmax iterations of tile t so far (phase of bar_p)
+      // Phase governor.  A tile's chain  softmax -> P seen -> PV + QK -> S seen  is what sets the period, and
+      // the two softmax warps of a sub-partition share its MUFU pipe: wherever the two tiles' softmax windows
+      // overlap, both slow down by nearly the overlap.  The offset between the tiles is neutrally stable (both
+      // pay the same penalty), so nothing pulls it to the overlap-free middle: measured 1320 / 2150 clk instead
+      // of 1740 / 1740, softmax 1900 clk instead of 1450.  The issuer therefore holds a tile's MMAs back until
+      // half the measured period (minus a margin that lets the estimate decay) has passed since it issued the
+      // other tile's.
+      [[maybe_unused]] uint32_t gov_t0 = 0, gov_t1 = 0, gov_half = 0;
       [[maybe_unused]] int trace_it = 0;
 #ifdef FA_TC5_TRACE
       if (p.trace && trace_cta) {   // SM clock vs wall clock over this CTA's whole life: effective frequency
@@ -412,6 +427,20 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
               // O_t (+)= P_t V_j : A = P (TMEM), B = V (MN-major, SW128); 8 k-steps of 16 keys
               mbar_wait(bar_p + 8 * t, (uint32_t)(((pbits >> t) ^ (j - jb_t)) & 1));
               TC5_TRACE(2, trace_it + j - j_begin, t * 8 + 2);
+#if FA_TC5_GOVERNOR
+              if constexpr (Cfg::TILES == 2) {
+                if (a0 && a1) {
+                  const uint32_t other = t == 0 ? gov_t1 : gov_t0;
+                  uint32_t now = clock32();
+                  if (gov_half) while ((int32_t)(now - other) < (int32_t)gov_half) now = clock32();
+                  if (t == 0) {
+                    const uint32_t per = now - gov_t0;              // tile 0 to tile 0
+                    if (j > j_begin && per < 16384u) gov_half = (per >> 1) - FA_TC5_GOV_MARGIN;
+                    gov_t0 = now;
+                  } else gov_t1 = now;
+                }
+              }
+#endif
               tc_fence_after();
               const uint32_t vb = ((kv_sm + vslot * Cfg::TILE_BYTES) & 0x3FFFF) >> 4;
 #pragma unroll
