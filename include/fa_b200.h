@@ -146,6 +146,19 @@ int fa_b200_fwd_kvcache(FaFwdParams* p, void* stream);
  * then runs fa_b200_fwd_kvcache with knew/vnew/rotary cleared, seqlen_knew kept, q = rotated q. */
 int fa_b200_append_kv(FaFwdParams* p, void* stream);
 
+/* fwd_kvcache for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.
+ * Same parameters and results as fa_b200_fwd_kvcache, except that p->workspace must be NULL and
+ * p->workspace_bytes 0: the split-KV partials (and the prefill work list, when a many-row call lands on
+ * the tcgen05 kernel) live in a static device array of FA_B200_STATIC_SCRATCH_BYTES inside the library,
+ * which every GPU that loads the library holds until exit.  A call that would need more is rejected with
+ * FA_ERR_WORKSPACE and a message stating both sizes; nothing is launched.  The entry point calls no
+ * cudaMalloc / cudaFree / allocating routine.  All calls share the array (it keeps the last call's
+ * contents; nothing in it has to start at zero): calls that overlap on the GPU race on it, so
+ * serialise them on one stream or use fa_b200_fwd_kvcache with separate workspaces. */
+#define FA_B200_STATIC_SCRATCH_BYTES (4u << 20)
+int fa_b200_fwd_kvcache_static_scratch(FaFwdParams* p, void* stream);
+
 /* Merge `n` partial results into o (rows,d) + lse (rows): lse = logsumexp_s lse_s,
  * o = sum_s exp(lse_s-lse) o_s — the algebra of combine_attn_seqk_parallel
  * (flash_fwd_kernel.h:1092-1250); used for the in-GPU split-KV merge and for the cross-GPU

@@ -389,3 +389,65 @@ extern "C" int fa_b200_exchange_combine(const FaExchangeParams* a, void* stream)
   return FA_OK;
 }
 extern "C" size_t fa_b200_exchange_params_size(void) { return sizeof(FaExchangeParams); }
+
+// ---------------------------------------------------------------------------------------------
+// fa_b200_fwd_kvcache_static_scratch — fwd_kvcache for callers that cannot allocate (CUDA-graph
+// capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same call as fa_b200_fwd_kvcache, but the split-KV
+// partials (lse_accum | o_accum) that fa_decode_kernel / fa_tile_kernel write and fa_combine_kernel
+// merges live in the file-scope device array below instead of a caller-allocated workspace.
+//   * Size: FA_B200_STATIC_SCRATCH_BYTES (4 MiB) — every GPU that loads the library holds it until exit.
+//     A call whose plan needs more is rejected (FA_ERR_WORKSPACE) before anything is launched.
+//   * The array's NAME is only a host-side stand-in in host code: its device address is fetched with
+//     cudaGetSymbolAddress once per device (that device current) and that pointer goes to the kernels.
+//   * Every call shares the array and finds the previous call's contents in it.  Nothing has to start
+//     at zero: every CTA of the split kernel writes its (split, row) slice, empty splits included
+//     (O = 0, lse = -inf), before the combine kernel of the same call reads it, and the prefill work
+//     list (when a many-row call lands on the tcgen05 kernel) is rebuilt by tc5_schedule_kernel, which
+//     also resets its draw counter.  Calls that OVERLAP on the GPU (different streams, or graphs
+//     replayed concurrently) race on the array: serialise them, or use fa_b200_fwd_kvcache with
+//     separate workspaces.
+//   * Calls no cudaMalloc / cudaFree / allocating library routine.
+static __device__ __align__(256) unsigned char g_static_scratch[FA_B200_STATIC_SCRATCH_BYTES];
+
+static int static_scratch_ptr(void** out) {
+  static void* ptrs[64] = {nullptr};           // per device; a racing first call stores the same value twice
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(FA_ERR_CUDA, "static scratch: cudaGetDevice failed: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= 64) return fail(FA_ERR_UNSUPPORTED, "static scratch: device index %d out of range", dev);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return fail(FA_ERR_CUDA, "static scratch: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return FA_OK;
+}
+
+extern "C" int fa_b200_fwd_kvcache_static_scratch(FaFwdParams* a, void* stream) {
+  g_err[0] = 0;
+  FA_CHECK(a != nullptr, "params is NULL");
+  FA_CHECK(a->workspace == nullptr && a->workspace_bytes == 0,
+           "fwd_kvcache_static_scratch takes no workspace: the scratch is the library's static device array");
+  Plan pl;
+  int rc = make_plan(a, OP_KVCACHE, &pl);
+  if (rc != FA_OK) return rc;
+  const size_t need = pl.ws_bytes ? pl.ws_bytes + 16 : 0;     // + alignment slack, as fa_b200_workspace_bytes reports
+  if (need > (size_t)FA_B200_STATIC_SCRATCH_BYTES)
+    return fail(FA_ERR_WORKSPACE, "fwd_kvcache_static_scratch: this call needs %zu bytes of scratch, the static maximum is %zu "
+                "(use fa_b200_fwd_kvcache with a caller-allocated workspace, or fewer splits)",
+                need, (size_t)FA_B200_STATIC_SCRATCH_BYTES);
+  void* ptr = nullptr;
+  if (need) {
+    rc = static_scratch_ptr(&ptr);
+    if (rc != FA_OK) return rc;
+  }
+  a->workspace = ptr;
+  a->workspace_bytes = need ? (size_t)FA_B200_STATIC_SCRATCH_BYTES : 0;
+  rc = run_plan(a, OP_KVCACHE, stream);
+  a->workspace = nullptr; a->workspace_bytes = 0;              // the caller's block stays as it was passed
+  return rc;
+}

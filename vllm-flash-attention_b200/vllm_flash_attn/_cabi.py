@@ -54,7 +54,9 @@ EXPORTS = (
     "fa_b200_num_splits_heuristic", "fa_b200_workspace_bytes",
     "fa_b200_fwd", "fa_b200_varlen_fwd", "fa_b200_fwd_kvcache", "fa_b200_combine",
     "fa_b200_append_kv", "fa_b200_exchange_combine", "fa_b200_exchange_params_size",
+    "fa_b200_fwd_kvcache_static_scratch",
 )
+STATIC_SCRATCH_BYTES = 4 << 20      # FA_B200_STATIC_SCRATCH_BYTES (include/fa_b200.h)
 
 
 FA_MAX_PEERS = 8
@@ -81,7 +83,8 @@ def _load():
     lib.fa_b200_num_splits_heuristic.argtypes = [C.c_int] * 4
     lib.fa_b200_workspace_bytes.restype = C.c_size_t
     lib.fa_b200_workspace_bytes.argtypes = [C.POINTER(FaFwdParams), C.c_int]
-    for name in ("fa_b200_fwd", "fa_b200_varlen_fwd", "fa_b200_fwd_kvcache", "fa_b200_append_kv"):
+    for name in ("fa_b200_fwd", "fa_b200_varlen_fwd", "fa_b200_fwd_kvcache", "fa_b200_append_kv",
+                 "fa_b200_fwd_kvcache_static_scratch"):
         fn = getattr(lib, name)
         fn.restype = C.c_int
         fn.argtypes = [C.POINTER(FaFwdParams), _vp]
