@@ -9,7 +9,11 @@ GQA 32q/8kv heads, D=128, 16 384 tokens over seqlens [8192,4096,2048,1024,512,25
 metric = attention forward TFLOP/s, FLOPs = 2*H*D*sum(s_i^2) (= 4*s^2*H*D/2 causal; reference
 benchmarks/benchmark_flash_attention.py:27-30).  N>1: head-sharded replicas of the same per-GPU
 work (each rank owns 32q/8kv heads of a 32N-head layer; no collective) -> weak scaling.
-The JSON line also carries the paged-KV decode figure (C3: B=256, ctx 4096, block 16) under "decode".
+The JSON line also carries the paged-KV decode figure (C3: B=256, ctx 4096, block 16) under "decode" and, at
+every N, the two shardings north_star names, strong-scaled against a 1-GPU run made in the same process:
+"c4" (64q/8kv heads head-sharded, mixed prefill+decode varlen batch, no collective) and "c5" (131072-token
+decode, KV sequence split over the ranks, (out,lse) exchanged by the fused peer-memory kernel or by one NCCL
+all-gather, then LSE-combined), each with parity_ok against the single-GPU result.
 """
 import argparse
 import json
@@ -141,27 +145,38 @@ def make_prefill_inputs(dev, seed=0):
     return q, k, v, cu
 
 
-def cpu_attention_sample(threads, budget_s=20.0):
+def cpu_attention_sample(threads, budget_s=60.0):
     """The reference's PyTorch attention_ref (our oracle port, oracle/attention_oracle.py) timed on the
-    host cores on a bounded sample of the C2 workload: whole sequences from the short end of the
-    batch, all 32 heads, causal, fp32 upcast.  Returns (tflops, description)."""
+    host cores over the WHOLE C2 batch: every sequence, all 32 heads, causal, fp32 upcast.  attention_ref
+    materialises (B,H,Sq,Sk) scores, so it runs per sequence and, from 2048 tokens up, per KV-head group
+    (4 query heads + their KV head: 1 GiB of fp32 scores at 8192 tokens) — SURVEY 8d's chunking.  If the
+    budget runs out the remaining sequences are skipped and the description says which ones ran.
+    Returns (tflops, description)."""
     import torch
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import attention_oracle as orc
     torch.set_num_threads(threads)
     g = torch.Generator().manual_seed(0)
     done_flops, t_total, used = 0.0, 0.0, []
-    for s in [128, 128, 256, 512, 1024, 2048]:
+    grp = H // HK
+    for s in sorted(SEQLENS_C2):
         q = torch.randn(1, s, H, D, generator=g).to(torch.bfloat16)
         k = torch.randn(1, s, HK, D, generator=g).to(torch.bfloat16)
         v = torch.randn(1, s, HK, D, generator=g).to(torch.bfloat16)
         t0 = time.perf_counter()
-        orc.attention_ref(q, k, v, causal=True)
+        if s >= 2048:
+            for kh in range(HK):
+                orc.attention_ref(q[:, :, kh * grp:(kh + 1) * grp], k[:, :, kh:kh + 1], v[:, :, kh:kh + 1], causal=True)
+        else:
+            orc.attention_ref(q, k, v, causal=True)
         dt = time.perf_counter() - t0
         done_flops += prefill_flops([s]); t_total += dt; used.append(s)
         if t_total > budget_s:
             break
-    return done_flops / t_total / 1e12, f"attention_ref (fp32 upcast) on sequences {used} of the C2 batch, 32q/8kv heads, causal"
+    whole = len(used) == len(SEQLENS_C2)
+    desc = ("attention_ref (fp32 upcast) over " + ("the whole C2 batch" if whole else f"sequences {used} of the C2 batch") +
+            ", 32q/8kv heads, causal; per sequence, and per KV-head group from 2048 tokens up")
+    return done_flops / t_total / 1e12, desc
 
 
 def run_reference(args):
@@ -173,11 +188,11 @@ def run_reference(args):
     import torch
     threads = os.cpu_count() or 1
     for _ in range(min(args.warmup, 1)):
-        cpu_attention_sample(threads, budget_s=2.0)
+        cpu_attention_sample(threads, budget_s=1.0)
     vals, desc = [], ""
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        v, desc = cpu_attention_sample(threads, budget_s=6.0)
+        v, desc = cpu_attention_sample(threads, budget_s=60.0)
         vals.append(v)
     ms = (time.perf_counter() - t0) / max(args.steps, 1) * 1e3
     val = sum(vals) / len(vals)
@@ -186,7 +201,7 @@ def run_reference(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": "C2 Llama-3-8B prefill: flash_attn_varlen_func causal GQA 32q/8kv D=128, 16384 tokens, "
                                    "seqlens " + str(SEQLENS_C2),
-                       "sample": "each step = a bounded sample of that workload on the host cores: " + desc},
+                       "sample": "each step = one pass over that workload on the host cores: " + desc},
             "cpu_baseline": {"value": val, "unit": "TFLOP/s", "cores": threads, "kind": "port", "sample": desc},
             "e2e": {"value": val, "unit": "TFLOP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -313,11 +328,13 @@ def run_ours(args):
                        "l2": "inputs+outputs 320 MiB per step > 126 MB L2", "kernel": {1: "tcgen05_prefill", 2: "tile_mma_sync", 3: "decode"}.get(kernel_used)},
             "e2e": {"value": e2e_value, "unit": "TFLOP/s", "h2d_bytes_per_step": (qh.numel() + kh.numel() + vh.numel()) * 2,
                     "d2h_bytes_per_step": out_h.numel() * 2, "ms_per_step": ms_e2e,
-                    "note": "pinned host q,k,v -> device, attention, out -> pinned host every step; 3 streams, double-buffered"},
+                    "note": "pinned host q,k,v -> device, attention, out -> pinned host every step; 3 streams, double-buffered" +
+                            ("; at N>1 every rank pushes its 335 MB per step through the host's PCIe roots at once, so this figure is "
+                             "bound by host PCIe / NUMA bandwidth, not by the kernels" if world > 1 else "")},
             "gpu_launches": launches_per_step * args.steps * 2,   # kernel-only region + e2e region
             "roofline": {"bound": "tensor", "achieved": per_gpu_tflops, "peak": pk["bf16_tflops"], "unit": "TFLOP/s",
                          "frac": per_gpu_tflops / pk["bf16_tflops"], "traffic": ncu_traffic("prefill_c2"), "peak_source": pk_src + " burst (cuBLAS bf16)",
-                         "frac_of_sustained": per_gpu_tflops / pk["bf16_tflops_sustained"], "frac_of_nominal_2250": per_gpu_tflops / 2250.0,
+                         "frac_of_nominal_2250": per_gpu_tflops / 2250.0,
                          "flops_per_launch": flops},
             "clocks": clocks}
     del bufs
@@ -325,9 +342,16 @@ def run_ours(args):
     # ------------------------------------------------------------------ paged decode (C3), rank-local
     if args.decode:
         line["decode"] = bench_decode(fa, ext, dev, pk, pk_src, args)
+    # ------------------------------------------------------------------ the two shardings (C4, C5), every N
+    if args.sharded:
+        torch.cuda.empty_cache()
+        line["c4"] = bench_c4(fa, ext, dev, world, rank, pk)
+        torch.cuda.empty_cache()
+        line["c5"] = {"b1": bench_c5(fa, ext, dev, world, rank, pk, batch=1), "b8": bench_c5(fa, ext, dev, world, rank, pk, batch=8)}
+        torch.cuda.empty_cache()
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        val, desc = cpu_attention_sample(threads, budget_s=15.0)
+        val, desc = cpu_attention_sample(threads, budget_s=30.0)
         line["cpu_baseline"] = {"value": val, "unit": "TFLOP/s", "cores": threads, "kind": "port", "sample": desc}
     if rank == 0:
         print(json.dumps(line), flush=True)
@@ -371,6 +395,233 @@ def bench_decode(fa, ext, dev, pk, pk_src, args, b=256, ctx=4096, page=16):
                          "bytes_per_launch": nbytes}}
 
 
+# ------------------------------------------------------------------------------------------------
+# The two shardings north_star names, measured at every N (strong scaling: the total work is fixed).
+def _timed(f, iters, world, dev, warmup=5):
+    """CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks -> ms per call."""
+    import torch
+    import torch.distributed as dist
+    for _ in range(warmup):
+        f()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        f()
+    e1.record()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
+
+
+def _timed_graph(f, iters, world, dev):
+    """The same measurement with the call captured in a CUDA graph (how a serving loop replays decode steps).
+    Every rank captures, so a failure on one rank is agreed on before anyone replays (no stuck collective)."""
+    import torch
+    import torch.distributed as dist
+    g, ok = None, 1
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                f()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            f()
+    except Exception as ex:  # noqa: BLE001
+        print("graph capture failed:", repr(ex)[:300], file=sys.stderr, flush=True)
+        ok = 0
+    t = torch.tensor([ok], device=dev, dtype=torch.int32)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if t.item() == 0:
+        return None
+    return _timed(g.replay, iters, world, dev)
+
+
+def bench_c4(fa, ext, dev, world, rank, pk, iters=20):
+    """C4 (BASELINE.json configs[3]): Llama-3-70B attention, 64q/8kv heads, D=128, head-sharded over
+    the ranks (no collective); ONE mixed varlen call through flash_attn_varlen_func(block_table=...): 4 prompts of
+    2048 tokens + 192 single-token decodes with contexts randint(1024, 4097), paged block 16, seed 0.
+    Strong scaling: t(1 GPU, all 64 heads) is measured on rank 0 in the same run."""
+    import torch
+    import torch.distributed as dist
+    from vllm_flash_attn import sharded
+    Hq, Hk, page, dt = 64, 8, 16, torch.bfloat16
+    n_pre, s_pre, n_dec = 4, 2048, 192
+    gc = torch.Generator(device="cpu").manual_seed(0)
+    dec_ctx = torch.randint(1024, 4097, (n_dec,), generator=gc).tolist()
+    q_lens, k_lens = [s_pre] * n_pre + [1] * n_dec, [s_pre] * n_pre + dec_ctx
+    acc = lambda xs: [0] + list(__import__("itertools").accumulate(xs))
+    cq = torch.tensor(acc(q_lens), dtype=torch.int32, device=dev)
+    ck = torch.tensor(acc(k_lens), dtype=torch.int32, device=dev)
+    tq, nb = sum(q_lens), len(q_lens)
+    max_blocks = (max(k_lens) + page - 1) // page
+    nblk = nb * max_blocks
+    g = torch.Generator(device=dev).manual_seed(0)            # same Philox stream on every rank's GPU: same tensors
+    q_all = torch.randn(tq, Hq, D, device=dev, dtype=dt, generator=g)
+    kc_all = torch.randn(nblk, page, Hk, D, device=dev, dtype=dt, generator=g)
+    vc_all = torch.randn(nblk, page, Hk, D, device=dev, dtype=dt, generator=g)
+    bt = torch.randperm(nblk, device=dev, generator=g).to(torch.int32).view(nb, max_blocks).contiguous()
+    qs, ks = sharded.head_shard(rank, world, Hq, Hk)
+    q_r, kc_r, vc_r = q_all[:, qs].contiguous(), kc_all[:, :, ks].contiguous(), vc_all[:, :, ks].contiguous()
+    mq, mk = max(q_lens), max(k_lens)
+    call = lambda q_, k_, v_: fa.flash_attn_varlen_func(q_, k_, v_, cq, ck, mq, mk, causal=True, block_table=bt)
+    # ---- single-GPU reference time and result (rank 0, all heads) ----
+    t1, o_full = None, None
+    if rank == 0:
+        o_full = call(q_all, kc_all, vc_all)
+    t1 = _timed(lambda: call(q_all, kc_all, vc_all), iters, 1, dev) if rank == 0 else 0.0
+    if world > 1:
+        if rank != 0:
+            del q_all, kc_all, vc_all
+        tt = torch.tensor([t1], device=dev, dtype=torch.float64)
+        dist.broadcast(tt, 0)
+        t1 = tt.item()
+    # ---- sharded run ----
+    o_r = call(q_r, kc_r, vc_r)
+    launches = ext.last_call_info.get("launches")
+    parity = None
+    if world > 1:
+        parts = [torch.empty_like(o_r) for _ in range(world)]
+        dist.all_gather(parts, o_r)                # check only: the product path has no collective
+        if rank == 0:
+            parity = (torch.cat(parts, dim=1).float() - o_full.float()).abs().max().item()
+    elif rank == 0:
+        parity = (o_r.float() - o_full.float()).abs().max().item()
+    tn = _timed(lambda: call(q_r, kc_r, vc_r), iters, world, dev)
+    # the two parts alone (same shard): prefill sequences only / decode sequences only
+    cq_p, ck_p = cq[: n_pre + 1].contiguous(), ck[: n_pre + 1].contiguous()
+    t_pre = _timed(lambda: fa.flash_attn_varlen_func(q_r[: n_pre * s_pre], kc_r, vc_r, cq_p, ck_p, s_pre, s_pre, causal=True,
+                                                     block_table=bt[:n_pre]), iters, world, dev)
+    cq_d = (cq[n_pre:] - cq[n_pre]).contiguous(); ck_d = (ck[n_pre:] - ck[n_pre]).contiguous()
+    t_dec = _timed(lambda: fa.flash_attn_varlen_func(q_r[n_pre * s_pre:], kc_r, vc_r, cq_d, ck_d, 1, max(dec_ctx), causal=True,
+                                                     block_table=bt[n_pre:]), iters, world, dev)
+    flops = 2.0 * Hq * D * n_pre * s_pre * s_pre                   # whole job, causal
+    nbytes = 2.0 * float(sum(dec_ctx)) * Hk * D * 2                # whole job, K+V of the decode sequences once
+    return {"workload": "C4 Llama-3-70B attention 64q/8kv D=128 head-sharded, one flash_attn_varlen_func(block_table) call: "
+                        "4x2048-token prompts + 192 decodes (ctx randint(1024,4097)), paged block 16, seed 0",
+            "n_gpus": world, "heads_per_gpu": [Hq // world, Hk // world], "scaling": "strong",
+            "ms": tn, "ms_1gpu_all_heads": t1, "speedup_vs_1gpu": t1 / tn, "strong_scaling_efficiency": t1 / (world * tn),
+            "ms_prefill_part_alone": t_pre, "ms_decode_part_alone": t_dec,
+            "prefill_part_tflops_per_gpu": flops / world / (t_pre * 1e-3) / 1e12,
+            "decode_part_gbs_per_gpu": nbytes / world / (t_dec * 1e-3) / 1e9,
+            "prefill_part_frac_of_peak": flops / world / (t_pre * 1e-3) / 1e12 / pk["bf16_tflops"],
+            "decode_part_frac_of_peak": nbytes / world / (t_dec * 1e-3) / 1e9 / pk["hbm_gbs"],
+            "launches_per_call": launches, "collective": "none (heads independent)",
+            "parity_max_abs_vs_1gpu": parity, "parity_ok": (parity is not None and parity <= 1e-6) if rank == 0 else None}
+
+
+def bench_c5(fa, ext, dev, world, rank, pk, batch, ctx=131072, iters=30):
+    """C5 (BASELINE.json configs[4]): long-context decode, 32q/8kv D=128, ctx 131072, paged block 16,
+    KV sequence split over the ranks (contiguous ctx/N keys per rank); per-rank (out fp32, lse) partials are
+    exchanged and LSE-combined (flash_fwd_kernel.h:1151-1221 lifted to ranks) by (a) ONE fused peer-memory
+    kernel (fa_b200_exchange_combine over NVLink) or (b) ONE NCCL all-gather + the combine kernel.
+    Strong scaling: t(1 GPU, whole sequence) is measured on rank 0 in the same run, eager and as a CUDA graph."""
+    import torch
+    import torch.distributed as dist
+    from vllm_flash_attn import sharded
+    page, dt = 16, torch.bfloat16
+    g = torch.Generator(device=dev).manual_seed(1234 + batch)
+    q = torch.randn(batch, 1, H, D, device=dev, dtype=dt, generator=g)
+    lens_h = [ctx] * batch
+    if batch > 1:
+        lens_h[1] = ctx // 3 + 5                   # one ragged sequence: some ranks hold none of it
+    lens = torch.tensor(lens_h, dtype=torch.int32, device=dev)
+    ranges = [sharded.seq_shard_range(r, world, ctx, page) for r in range(world)]
+    ranges = [(s, min(e, ctx)) for s, e in ranges]
+
+    def shard_kv(r, which):                        # keys [s, e) of every sequence, reproducible on any rank's GPU
+        s, e = ranges[r]
+        gg = torch.Generator(device=dev).manual_seed(100000 * which + 10 * batch + r)
+        return torch.randn(batch, e - s, HK, D, device=dev, dtype=dt, generator=gg)
+
+    s, e = ranges[rank]
+    L = e - s
+    nblk = batch * (L // page)
+    gp = torch.Generator(device=dev).manual_seed(77 + rank)
+    bt = torch.randperm(nblk, device=dev, generator=gp).to(torch.int32).view(batch, L // page).contiguous()
+    kc = torch.empty(nblk, page, HK, D, device=dev, dtype=dt); vc = torch.empty_like(kc)
+    kc[bt.view(-1).long()] = shard_kv(rank, 0).view(nblk, page, HK, D)
+    vc[bt.view(-1).long()] = shard_kv(rank, 1).view(nblk, page, HK, D)
+    nbytes = 2.0 * float(sum(lens_h)) * HK * D * 2             # whole job: K+V of every sequence once
+
+    # ---- single-GPU reference (rank 0): the whole sequence in one paged pool, auto split-KV ----
+    t1 = t1g = 0.0
+    o1 = l1 = None
+    splits1 = None
+    if rank == 0:
+        nb1 = batch * (ctx // page)
+        bt1 = torch.randperm(nb1, device=dev, generator=gp).to(torch.int32).view(batch, ctx // page).contiguous()
+        kf = torch.empty(nb1, page, HK, D, device=dev, dtype=dt); vf = torch.empty_like(kf)
+        kf[bt1.view(-1).long()] = torch.cat([shard_kv(r, 0) for r in range(world)], dim=1).view(nb1, page, HK, D)
+        vf[bt1.view(-1).long()] = torch.cat([shard_kv(r, 1) for r in range(world)], dim=1).view(nb1, page, HK, D)
+        f1 = lambda: fa.flash_attn_with_kvcache(q, kf, vf, cache_seqlens=lens, block_table=bt1, causal=True, return_softmax_lse=True)
+        o1, l1 = f1()
+        splits1 = ext.last_call_info.get("num_splits")
+        t1 = _timed(f1, iters, 1, dev)
+        t1g = _timed_graph(f1, iters, 1, dev) or 0.0
+        del kf, vf
+    if world > 1:
+        tt = torch.tensor([t1, t1g], device=dev, dtype=torch.float64)
+        dist.broadcast(tt, 0)
+        t1, t1g = tt[0].item(), tt[1].item()
+    res = {"workload": f"C5 long-context decode: flash_attn_with_kvcache, B={batch}, ctx {ctx}, 32q/8kv D=128, paged block {page}, "
+                       "KV sequence split over the ranks + (out,lse) exchange + LSE combine",
+           "n_gpus": world, "batch": batch, "scaling": "strong", "bytes_whole_job": nbytes,
+           "ms_1gpu": t1, "ms_1gpu_cuda_graph": t1g or None, "num_splits_1gpu": splits1,
+           "gbs_1gpu": nbytes / (t1 * 1e-3) / 1e9, "gbs_1gpu_cuda_graph": (nbytes / (t1g * 1e-3) / 1e9) if t1g else None,
+           "frac_of_hbm_peak_1gpu_cuda_graph": (nbytes / (t1g * 1e-3) / 1e9 / pk["hbm_gbs"]) if t1g else None}
+    if world == 1:
+        res.update({"ms": t1, "ms_cuda_graph": t1g or None, "parity_ok": True, "collective": "none (one GPU: in-GPU split-KV + combine)"})
+        return res
+
+    # ---- sharded: (a) fused peer-memory exchange, (b) NCCL all-gather + combine ----
+    xch = sharded.PeerExchange(sharded.partial_record_numel(batch, 1, H, D), dev)
+    f_fused = lambda: sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
+                                                                   return_softmax_lse=True, exchange=xch)
+    f_nccl = lambda: sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
+                                                                  return_softmax_lse=True)
+    of, lf = f_fused()
+    on, ln = f_nccl()
+    splits_n = ext.last_call_info.get("num_splits")
+    torch.cuda.synchronize()
+    par = None
+    if rank == 0:
+        par = {"fused_out": (of.float() - o1.float()).abs().max().item(), "fused_lse": (lf - l1).abs().max().item(),
+               "nccl_out": (on.float() - o1.float()).abs().max().item(), "nccl_lse": (ln - l1).abs().max().item()}
+    t_f = _timed(f_fused, iters, world, dev)
+    t_n = _timed(f_nccl, iters, world, dev)
+    t_fg = _timed_graph(f_fused, iters, world, dev)
+    t_ng = _timed_graph(f_nccl, iters, world, dev)
+    lens_local = sharded.seq_shard_lengths(lens, s, e)
+    t_loc = _timed_graph(lambda: sharded.kvcache_partial(q, kc, vc, lens_local, bt), iters, world, dev)
+    best = min(x for x in (t_f, t_n, t_fg, t_ng) if x)
+    t1_best = min(x for x in (t1, t1g) if x)
+    res.update({
+        "ms_fused_exchange": t_f, "ms_nccl_allgather": t_n, "ms_fused_exchange_cuda_graph": t_fg, "ms_nccl_allgather_cuda_graph": t_ng,
+        "ms_local_split_decode_only_cuda_graph": t_loc, "num_splits_per_rank": splits_n,
+        "ms": best, "speedup_vs_1gpu": t1_best / best, "strong_scaling_efficiency": t1_best / (world * best),
+        "gbs_per_gpu": nbytes / world / (best * 1e-3) / 1e9, "frac_of_hbm_peak_per_gpu": nbytes / world / (best * 1e-3) / 1e9 / pk["hbm_gbs"],
+        "gbs_per_gpu_local_kernel_only": (nbytes / world / (t_loc * 1e-3) / 1e9) if t_loc else None,
+        "exchange_bytes_per_rank": sharded.partial_record_numel(batch, 1, H, D) * 4 * (world - 1),
+        "collective": "fa_b200_exchange_combine (peer-memory stores over NVLink, one kernel) | NCCL all_gather_into_tensor + fa_b200_combine",
+        "parity_max_abs_vs_1gpu": par,
+        # bf16 output of two different split trees (ranks x splits vs splits): one bf16 ulp at |o| < 4
+        "parity_ok": (max(par["fused_out"], par["nccl_out"]) <= 2e-2 and max(par["fused_lse"], par["nccl_lse"]) <= 1e-3) if rank == 0 else None})
+    del xch
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -379,6 +630,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-decode", dest="decode", action="store_false")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-sharded", dest="sharded", action="store_false", help="skip the C4 / C5 sub-benchmarks")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

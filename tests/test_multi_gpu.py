@@ -1,0 +1,101 @@
+"""GPU, 2 ranks (skipped with fewer than 2 devices; run with `gpurun --gpus 2`): the two shardings on real
+GPUs, one process per GPU over NCCL.
+* sequence-sharded decode through BOTH exchanges (fused peer-memory kernel / NCCL all-gather + combine) against
+  the single-GPU kernel over the whole sequence, with the batch size ALTERNATING between calls through one
+  PeerExchange — the continuous-batching pattern in which per-CTA protocol state could drift apart;
+* head-sharded mixed prefill+decode varlen batch against rank 0 running all heads.
+The reference has no multi-GPU attention path; the algebra checked is combine_attn_seqk_parallel's
+(flash_fwd_kernel.h:1151-1221) lifted from splits to ranks."""
+import os
+import socket
+
+import pytest
+import torch
+
+import _util  # noqa: F401  (sys.path)
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
+
+
+def _worker(rank, world, port, ret):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import sharded
+    dt, H, HK, D, page = torch.bfloat16, 32, 8, 128, 16
+    errs = {}
+    try:
+        # ---------------- sequence-sharded decode, alternating batch sizes through ONE PeerExchange
+        ctx = 8192
+        s, e = sharded.seq_shard_range(rank, world, ctx, page)
+        e = min(e, ctx)
+        L = e - s
+        xch = sharded.PeerExchange(sharded.partial_record_numel(8, 1, H, D), dev)
+        for step, b in enumerate([1, 4, 1, 8, 3, 8, 1, 1, 5, 2, 8, 1]):
+            g = torch.Generator(device="cpu").manual_seed(1000 + step)          # same data on every rank
+            q = torch.randn(b, 1, H, D, generator=g).to(dt).to(dev)
+            kfull = torch.randn(b, ctx, HK, D, generator=g).to(dt)
+            vfull = torch.randn(b, ctx, HK, D, generator=g).to(dt)
+            lens = torch.randint(1, ctx + 1, (b,), generator=g).to(torch.int32)
+            lens[0] = ctx
+            lens = lens.to(dev)
+            nblk = b * (L // page)
+            bt = torch.randperm(nblk, generator=g).view(b, L // page).to(torch.int32).to(dev)
+            kc = torch.empty(nblk, page, HK, D, dtype=dt, device=dev); vc = torch.empty_like(kc)
+            kc[bt.view(-1).long()] = kfull[:, s:e].reshape(nblk, page, HK, D).to(dev)
+            vc[bt.view(-1).long()] = vfull[:, s:e].reshape(nblk, page, HK, D).to(dev)
+            of, lf = sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
+                                                                  return_softmax_lse=True, exchange=xch)
+            on, ln = sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
+                                                                  return_softmax_lse=True)
+            o1, l1 = fa.flash_attn_with_kvcache(q, kfull.to(dev), vfull.to(dev), cache_seqlens=lens, causal=True,
+                                                return_softmax_lse=True)
+            torch.cuda.synchronize()
+            errs[f"seq{step}_b{b}"] = (max((of.float() - o1.float()).abs().max().item(), (on.float() - o1.float()).abs().max().item()),
+                                       max((lf - l1).abs().max().item(), (ln - l1).abs().max().item()),
+                                       (of.float() - on.float()).abs().max().item())
+        # ---------------- head-sharded mixed batch
+        Hq = 16
+        qs, ks = sharded.head_shard(rank, world, Hq, HK // 2)
+        g = torch.Generator(device="cpu").manual_seed(4321)
+        q_lens, k_lens = [300, 1, 1, 700, 1], [300, 513, 1200, 700, 64]
+        cq = torch.tensor([0] + list(torch.tensor(q_lens).cumsum(0)), dtype=torch.int32).to(dev)
+        ck = torch.tensor([0] + list(torch.tensor(k_lens).cumsum(0)), dtype=torch.int32).to(dev)
+        mb = (max(k_lens) + page - 1) // page
+        nblk = len(q_lens) * mb
+        q_all = torch.randn(sum(q_lens), Hq, D, generator=g).to(dt).to(dev)
+        kc_all = torch.randn(nblk, page, HK // 2, D, generator=g).to(dt).to(dev)
+        vc_all = torch.randn(nblk, page, HK // 2, D, generator=g).to(dt).to(dev)
+        bt = torch.randperm(nblk, generator=g).view(len(q_lens), mb).to(torch.int32).to(dev)
+        o_r = fa.flash_attn_varlen_func(q_all[:, qs].contiguous(), kc_all[:, :, ks].contiguous(), vc_all[:, :, ks].contiguous(),
+                                        cq, ck, max(q_lens), max(k_lens), causal=True, block_table=bt)
+        parts = [torch.empty_like(o_r) for _ in range(world)]
+        dist.all_gather(parts, o_r)
+        o_full = fa.flash_attn_varlen_func(q_all, kc_all, vc_all, cq, ck, max(q_lens), max(k_lens), causal=True, block_table=bt)
+        errs["head_sharded"] = ((torch.cat(parts, dim=1).float() - o_full.float()).abs().max().item(), 0.0, 0.0)
+        if rank == 0:
+            ret.update(errs)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs (gpurun --gpus 2)")
+def test_two_rank_shardings_match_single_gpu():
+    import torch.multiprocessing as mp
+    mgr = mp.Manager()
+    ret = mgr.dict()
+    mp.spawn(_worker, args=(2, _free_port(), ret), nprocs=2, join=True)
+    assert "head_sharded" in ret and len(ret) == 13
+    for name, (eo, el, ed) in ret.items():
+        if name == "head_sharded":
+            assert eo == 0.0, (name, eo)                   # heads are independent: bit-identical
+        else:
+            # two split trees (ranks x splits vs splits) of the same fp32 partials, output rounded to bf16 once
+            assert eo <= 2e-2 and el <= 1e-3 and ed <= 2e-2, (name, eo, el, ed)

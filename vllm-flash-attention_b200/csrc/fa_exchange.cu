@@ -14,13 +14,18 @@
 //   1. copy its rows (O row + lse) of the local record to recv[n&1][rank] of every rank (incl. self), fence
 //      system-wide, store n into flags[rank][c] of every rank;
 //   2. wait until flags[r][c] >= n for all r (one polling thread per peer), merge its rows from recv[n&1][*].
-// No count over the CTAs of a rank, no second fence, no CTA waits for data it does not merge.  A rank cannot
-// run two calls ahead of a peer (its call n+1 needs the peer's flag n+1, sent only after the peer finished
+// No count over the CTAs of a rank, no second fence, no CTA waits for data it does not merge.  All FA_XCHG_CTAS
+// CTAs run in every call (idle ones only exchange flags), so their call numbers stay in lockstep whatever
+// sequence of shapes is merged.  A rank cannot run two calls ahead of a peer (its call n+1 needs the peer's flag n+1, sent only after the peer finished
 // call n), so two receive buffers suffice.  All state lives in device memory: the launch is CUDA-graph
-// replayable.  The wait is bounded (trap after ~4 s) so that a missing peer surfaces as a launch failure,
+// replayable.  The wait is bounded (trap after FA_XCHG_TIMEOUT_NS = 120 s; all ranks should be warmed up before the first merge) so that a missing peer surfaces as a launch failure,
 // not a hung GPU.
 #include "fa_common.cuh"
 #include "fa_launch.h"
+
+#ifndef FA_XCHG_TIMEOUT_NS
+#define FA_XCHG_TIMEOUT_NS 120000000000ll   /* a peer may be late by a module load, a graph capture or a host stall; a MISSING peer still ends in a launch failure, not a hung GPU */
+#endif
 
 namespace fa {
 
@@ -78,7 +83,7 @@ __global__ void __launch_bounds__(256) fa_exchange_combine_kernel(const __grid_c
     while ((int)(ld_acquire_sys(p.flags[p.rank] + r * FA_XCHG_CTAS + cta) - n) < 0) {
       long long t1;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-      if (t1 - t0 > 4000000000ll) __trap();
+      if (t1 - t0 > FA_XCHG_TIMEOUT_NS) __trap();
     }
   }
   if (threadIdx.x == 0) p.state[cta] = n;
@@ -138,11 +143,14 @@ cudaError_t launch_exchange_combine(const FaExchangeParams& a, cudaStream_t stre
   p.o_batch_stride = a.o_batch_stride; p.o_row_stride = a.o_row_stride; p.o_head_stride = a.o_head_stride;
   p.out_dtype = a.out_dtype;
   const int64_t rows = (int64_t)a.b * a.h * a.seqlen_q;
-  // every CTA has to be resident while it waits for the peers: keep the grid far below one wave
-  int grid = (int)((rows + 7) / 8);
-  if (grid > FA_XCHG_CTAS) grid = FA_XCHG_CTAS;
-  if (grid < 1) grid = 1;
-  fa_exchange_combine_kernel<<<grid, 256, 0, stream>>>(p);
+  // Always FA_XCHG_CTAS CTAs, whatever the shape: the protocol state (call number, receive-buffer parity) is kept
+  // per CTA, so every CTA must take part in every call — a CTA without rows still publishes and waits for its
+  // flags.  With a shape-dependent grid the CTAs' call numbers drift apart when the batch size changes between
+  // calls (continuous batching) and a fast rank's call n+1 could overwrite the buffer half a slow peer is still
+  // merging for call n.  Every CTA has to be resident while it waits for the peers: 64 CTAs of 256 threads are
+  // far below one wave.
+  (void)rows;
+  fa_exchange_combine_kernel<<<FA_XCHG_CTAS, 256, 0, stream>>>(p);
   return cudaGetLastError();
 }
 
