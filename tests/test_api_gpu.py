@@ -322,12 +322,12 @@ def test_varlen_empty_sequences_through_the_work_list():
     src/block_info.h:11-42): no work unit for empty q, O = 0 for empty k; the batch is large enough
     (> 148 units) that the persistent kernel runs from the device-built work list."""
     info = _varlen_check([600, 0, 1, 257, 0, 128, 300, 513, 40], [600, 50, 700, 257, 0, 0, 300, 513, 900], h=16, hk=4)
-    assert info["kernel_used"] == 1 and info["launches"] == 3     # schedule + prefill + decode
+    assert info["kernel_used"] == 1 and info["launches"] == 4     # schedule + prefill + decode (16-row form) + decode (32-row form)
     info = _varlen_check([130, 0, 70], [130, 64, 0], h=4, hk=4, causal=False)
     assert info["kernel_used"] == 1
     # one-tile units (d > 128): 128-row work units, Q through the K/V ring, empty rows / sequences in between
     info = _varlen_check([600, 0, 1, 257, 0, 128, 300, 513, 40], [600, 50, 700, 257, 0, 0, 300, 513, 900], h=16, hk=4, d=256)
-    assert info["kernel_used"] == 1 and info["launches"] == 3
+    assert info["kernel_used"] == 1 and info["launches"] == 3     # d > 128: the decode kernel holds 16 packed rows, one form
     info = _varlen_check([130, 0, 70, 300], [130, 64, 0, 200], h=4, hk=2, d=192)
     assert info["kernel_used"] == 1
 
@@ -342,7 +342,7 @@ def test_varlen_many_sequences_mixed():
     for i, s in ((7, 1100), (400, 700), (1499, 300)):
         lens_q[i] = s; lens_k[i] = s + 100
     info = _varlen_check(lens_q, lens_k, h=8, hk=2, seed=1)
-    assert info["kernel_used"] == 1 and info["launches"] == 3
+    assert info["kernel_used"] == 1 and info["launches"] == 4
 
 
 def test_fused_exchange_single_rank_protocol():
@@ -382,16 +382,49 @@ def test_varlen_seqused_k():
     q = torch.randn(sum(lens_q), h, d, device=dev, dtype=dt)
     k = torch.randn(sum(lens_k), hk, d, device=dev, dtype=dt); v = torch.randn_like(k)
     su = torch.tensor(used, dtype=torch.int32, device=dev)
-    res = ext.varlen_fwd(q, k, v, None, cu_q.to(dev), cu_k.to(dev), su, None, None, max(lens_q), max(lens_k), 0.0,
+    kp, vp = k.clone(), v.clone()
+    for i in range(3):          # rows past seqused_k hold NaN: they must never reach the output (0 * NaN in P.V)
+        kp[int(cu_k[i]) + used[i]:int(cu_k[i + 1])] = float("nan"); vp[int(cu_k[i]) + used[i]:int(cu_k[i + 1])] = float("nan")
+    res = ext.varlen_fwd(q, kp, vp, None, cu_q.to(dev), cu_k.to(dev), su, None, None, max(lens_q), max(lens_k), 0.0,
                          d ** -0.5, False, True, -1, -1, False, None)
     out = res[0]
-    assert ext.last_call_info["kernel_used"] == 1 and ext.last_call_info["launches"] == 2
+    assert not torch.isnan(out.float()).any()
+    assert ext.last_call_info["kernel_used"] == 1 and ext.last_call_info["launches"] == 3     # prefill + decode (16- and 32-row forms)
     # oracle: the same batch with k, v physically cut to the used lengths
     kc = torch.cat([k[int(cu_k[i]):int(cu_k[i]) + used[i]] for i in range(3)])
     vc = torch.cat([v[int(cu_k[i]):int(cu_k[i]) + used[i]] for i in range(3)])
     cu_u = torch.tensor([0] + used).cumsum(0).to(torch.int32)
     ref32, _ = orc.attention_ref_varlen(q, kc, vc, cu_q, cu_u, causal=True)
     pt, _ = orc.attention_ref_varlen(q, kc, vc, cu_q, cu_u, causal=True, upcast=False, reorder_ops=True)
+    err, err_pt = (out.float() - ref32.float()).abs().max().item(), (pt.float() - ref32.float()).abs().max().item()
+    assert err <= 2 * err_pt + 1e-5, (err, err_pt)
+
+
+@pytest.mark.parametrize("d", [64, 128, 256])
+@pytest.mark.parametrize("causal", [True, False])
+def test_varlen_neighbour_rows_do_not_leak_into_pv(d, causal):
+    """Packed varlen K/V: the 128-key V tile that holds the end of a sequence also holds the NEXT sequence's rows.
+    Their P is 0, but 0 * NaN = NaN, so one request's non-finite V would poison its neighbour's output unless the
+    kernel keeps those rows out of P.V (the reference zero-fills them: Clear_OOB_MN=true, flash_fwd_kernel.h:292).
+    Sequences 1 and 3 have no query rows and all-NaN K/V; every other sequence ends inside a tile they share."""
+    import vllm_flash_attn as fa
+    torch.manual_seed(11)
+    dev, dt, h, hk = "cuda", torch.bfloat16, 4, 2
+    lens_q = [200, 0, 333, 0, 129]
+    lens_k = [200, 100, 333, 300, 129]
+    cu_q = torch.tensor([0] + lens_q).cumsum(0).to(torch.int32); cu_k = torch.tensor([0] + lens_k).cumsum(0).to(torch.int32)
+    q = torch.randn(sum(lens_q), h, d, device=dev, dtype=dt)
+    k = torch.randn(sum(lens_k), hk, d, device=dev, dtype=dt); v = torch.randn_like(k)
+    kp, vp = k.clone(), v.clone()
+    for i in (1, 3):
+        kp[int(cu_k[i]):int(cu_k[i + 1])] = float("nan"); vp[int(cu_k[i]):int(cu_k[i + 1])] = float("nan")
+    out = fa.flash_attn_varlen_func(q, kp, vp, cu_q.to(dev), cu_k.to(dev), max(lens_q), max(lens_k), causal=causal)
+    assert _ext().last_call_info["kernel_used"] == 1
+    assert not torch.isnan(out.float()).any()
+    clean = fa.flash_attn_varlen_func(q, k, v, cu_q.to(dev), cu_k.to(dev), max(lens_q), max(lens_k), causal=causal)
+    assert torch.equal(out, clean)          # the neighbours' contents make no difference at all
+    ref32, _ = orc.attention_ref_varlen(q, k, v, cu_q, cu_k, causal=causal)
+    pt, _ = orc.attention_ref_varlen(q, k, v, cu_q, cu_k, causal=causal, upcast=False, reorder_ops=True)
     err, err_pt = (out.float() - ref32.float()).abs().max().item(), (pt.float() - ref32.float()).abs().max().item()
     assert err <= 2 * err_pt + 1e-5, (err, err_pt)
 

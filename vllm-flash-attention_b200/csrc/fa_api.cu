@@ -9,6 +9,9 @@
 #include <cstdio>
 #include <climits>
 #include <cstring>
+#include <map>
+#include <mutex>
+#include <utility>
 #include <vector>
 #include "fa_b200.h"
 #include "fa_launch.h"
@@ -74,6 +77,27 @@ static bool as_single_page(const FaFwdParams* a, int op, KParams* k) {
   if (!tc5_supported(t)) return false;
   *k = t;
   return true;
+}
+
+// Side stream + fork / join events for the decode half of a mixed varlen batch, one set per (device, caller
+// stream).  Created on first use and kept for the life of the process (a handful of streams in practice).
+// The fork / join pattern is capture-safe: under stream capture the side stream joins the capture at the fork
+// event and leaves it at the join event.
+struct ForkSet { cudaStream_t side; cudaEvent_t fork, join; };
+static ForkSet* get_fork_set(cudaStream_t main) {
+  static std::mutex mu;
+  static std::map<std::pair<int, cudaStream_t>, ForkSet> sets;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+  std::lock_guard<std::mutex> lock(mu);
+  auto key = std::make_pair(dev, main);
+  auto it = sets.find(key);
+  if (it != sets.end()) return &it->second;
+  ForkSet f;
+  if (cudaStreamCreateWithFlags(&f.side, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+  if (cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&f.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+  return &sets.emplace(key, f).first->second;
 }
 
 struct Plan {
@@ -237,8 +261,7 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
   switch (pl.kernel) {
     case FA_KERNEL_DECODE: e = launch_decode(k, pl.is_bf16, stream); break;
     case FA_KERNEL_TILE: e = launch_tile(k, pl.is_bf16, stream); break;
-    case FA_KERNEL_TC5_PREFILL:
-      if (pl.decode_rows > 0) k.min_rows = pl.decode_rows + 1;
+    case FA_KERNEL_TC5_PREFILL: {
       if (pl.ws_bytes) {
         if (a->workspace == nullptr || a->workspace_bytes < pl.ws_bytes)
           return fail(FA_ERR_WORKSPACE, "work-list workspace too small: need %zu bytes, got %zu", pl.ws_bytes, a->workspace_bytes);
@@ -246,14 +269,43 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
         k.work_header = reinterpret_cast<int*>(a->workspace);
         k.work_items = reinterpret_cast<int2*>(reinterpret_cast<char*>(a->workspace) + 16);
       }
-      e = launch_prefill_tc5(k, pl.is_bf16, a->total_q, a->total_k, pl.num_sms, stream);
       a->launches = pl.ws_bytes ? 1 : 0;
-      if (e == cudaSuccess && pl.decode_rows > 0) {
-        k.min_rows = 0; k.max_rows = pl.decode_rows;
-        e = launch_decode(k, pl.is_bf16, stream);
-        a->launches += 1;
+      // ---- decode half of a mixed batch: forked onto a side stream, ahead of the prefill launches.  A batch
+      // without short sequences (a plain prefill) then pays nothing on its own stream for the decode launches that
+      // find no work, and in a mixed batch the tails of the two halves overlap instead of running back to back.
+      ForkSet* fs = nullptr;
+      if (pl.decode_rows > 0) {
+        // The decode kernel is instantiated for 16 and for 32 packed rows (the 32-row form holds twice the Q / O
+        // fragments: fewer CTAs per SM and twice the MMA work per key).  Packed row counts are multiples of the
+        // group size, so the sequences of a mixed batch are served by the 16-row form wherever they fit — single-token
+        // decodes of any model with group <= 16 — and a second, 32-row launch is made only if some seqlen_q can give
+        // 17..32 packed rows at all.
+        const int cap = pl.decode_rows, g = k.group;
+        const int lo_rows = std::min(cap, 16);
+        bool second = false;
+        for (int sq = 1; sq <= a->seqlen_q && sq * g <= cap; sq++) second |= sq * g > lo_rows;
+        fs = get_fork_set(stream);
+        cudaStream_t ds = stream;
+        if (fs && cudaEventRecord(fs->fork, stream) == cudaSuccess && cudaStreamWaitEvent(fs->side, fs->fork, 0) == cudaSuccess) ds = fs->side;
+        else fs = nullptr;                              // no side stream: same launches, in order, on the caller's stream
+        KParams kd = k;
+        if (g <= lo_rows) {
+          kd.min_rows = 0; kd.max_rows = lo_rows;
+          e = launch_decode(kd, pl.is_bf16, ds);
+          a->launches += 1;
+        }
+        if (e == cudaSuccess && second) {
+          kd.min_rows = lo_rows + 1; kd.max_rows = cap;
+          e = launch_decode(kd, pl.is_bf16, ds);
+          a->launches += 1;
+        }
+        if (fs && cudaEventRecord(fs->join, fs->side) != cudaSuccess) return fail(FA_ERR_CUDA, "mixed batch: event record failed");
+        k.min_rows = cap + 1;
       }
+      if (e == cudaSuccess) e = launch_prefill_tc5(k, pl.is_bf16, a->total_q, a->total_k, pl.num_sms, stream);
+      if (fs && cudaStreamWaitEvent(stream, fs->join, 0) != cudaSuccess) return fail(FA_ERR_CUDA, "mixed batch: join failed");
       break;
+    }
     default: return fail(FA_ERR_INVALID, "unknown kernel id %d", pl.kernel);
   }
   if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in attention kernel launch: %s", cudaGetErrorString(e));

@@ -253,19 +253,50 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
         __syncwarp();
       }
       if constexpr (!PAGED) {
+        // Packed varlen K/V (and seqused_k): the V tile that holds the end of the sequence also holds rows of the NEXT
+        // sequence (or rows past seqused_k).  P is 0 there, but 0 * NaN/Inf would poison P.V with another request's
+        // data, so that one tile is filled by hand — valid rows copied, the rest zeroed, in the swizzle TMA would have
+        // used — like the paged tail below (the reference zero-fills them: Clear_OOB_MN, flash_fwd_kernel.h:292).
+        // Dense tensors need nothing: the tensor map ends at seqlen_k and TMA zero-fills beyond it.
+        // Only the unit's LAST V tile can be such a tile, so the issue loop (one lane) is left as it is and stops one
+        // item early when that tile needs the hand fill.
+        const int valid_last = sk - (j_end - 1) * TC5_BN;                // rows of the last tile inside the sequence
+        const bool tail = j_end > j_begin && valid_last < TC5_BN && (p.cu_seqlens_k != nullptr || p.seqused_k != nullptr);
         if (lane == 0) {
           for (int j = j_begin; j < j_end; j++) {
-            for (int kv = 0; kv < 2; kv++, ring++) {
+            for (int kv = 0; kv < 2; kv++) {
+              if (tail && kv == 1 && j == j_end - 1) break;
               const int slot = ring % NS, round = ring / NS;
               mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
               mbar_expect_tx(bar_kv_full + 8 * slot, Cfg::TILE_BYTES);
               for (int c = 0; c < ND; c++)
                 tma_load_4d(kv_sm + slot * Cfg::TILE_BYTES + c * Cfg::SUB_BYTES, kv == 0 ? &maps.k : &maps.v,
                             bar_kv_full + 8 * slot, c * 64, kvh, wk.k_row0 + j * TC5_BN, p.cu_seqlens_k ? 0 : wk.bidb);
+              ring++;
             }
           }
         }
         ring = __shfl_sync(0xffffffffu, ring, 0);
+        if (tail) {
+          const int slot = ring % NS, round = ring / NS;
+          const uint32_t dst = kv_sm + slot * Cfg::TILE_BYTES;
+          if (lane == 0) mbar_wait(bar_kv_empty + 8 * slot, (round & 1) ^ 1);
+          __syncwarp();
+          const T* vrow0 = reinterpret_cast<const T*>(p.v) + (int64_t)kvh * p.v_head_stride +
+                           (p.cu_seqlens_k ? (int64_t)0 : (int64_t)wk.bidb * p.v_batch_stride) +
+                           (int64_t)(wk.k_row0 + (j_end - 1) * TC5_BN) * p.v_row_stride;
+          for (int idx = lane; idx < TC5_BN * ND * 8; idx += 32) {
+            const int ch = idx & 7, c = (idx >> 3) % ND, r = (idx >> 3) / ND;
+            uint4 val = make_uint4(0, 0, 0, 0);
+            if (r < valid_last && c * 64 + ch * 8 < p.d) val = *reinterpret_cast<const uint4*>(vrow0 + (int64_t)r * p.v_row_stride + c * 64 + ch * 8);
+            asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst + c * Cfg::SUB_BYTES + r * 128 + ((ch ^ (r & 7)) << 4)),
+                         "r"(val.x), "r"(val.y), "r"(val.z), "r"(val.w) : "memory");
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_kv_full + 8 * slot);           // no TMA bytes outstanding: the plain arrival completes the phase
+          ring++;
+        }
       } else {
         // Paged K/V (reference src/utils.h:297-315, kernel_traits.h:136-144): a 128-key tile is
         // 128/box pages (or a slice of one big page); lane L looks up the block id of box L in the
@@ -501,12 +532,30 @@ tc5_schedule_kernel(const __grid_constant__ KParams p, int2* items, int* header,
     return min((a.je - a.jb) + (b.je - b.jb), TC5_SCHED_BINS - 1);
   };
   auto live = [&](int sq) { const int rows = sq * p.group; return sq > 0 && rows >= p.min_rows && rows <= p.max_rows; };
-  for (int s = tid; s < p.b; s += TC5_SCHED_THREADS) {
-    const SeqInfo si(p, s);
-    if (!live(si.sq)) continue;
-    const int n = (si.sq + unit_rows - 1) / unit_rows;
-    for (int mb = 0; mb < n; mb++) atomicAdd(&bins[TC5_SCHED_BINS - 1 - cost_of(mb, si.sq, si.sk)], 1);   // bin 0 = most expensive
-  }
+  // The (sequence, m_block) pairs are walked flat — pair idx = s * max_mb + mb with max_mb from the caller's
+  // max_seqlen_q — so that a batch of a few long sequences is spread over all threads instead of one thread
+  // looping over each sequence's blocks (C2: 8 sequences, up to 32 blocks).  The thread that holds a sequence's
+  // last regular block also walks any blocks beyond max_mb (a sequence longer than the stated maximum), and
+  // very ragged batches (many sequences, one long) fall back to one thread per sequence.
+  const int max_mb = max((p.seqlen_q + unit_rows - 1) / unit_rows, 1);
+  const bool flat = (int64_t)p.b * max_mb <= 16 * TC5_SCHED_THREADS;
+  const int n_idx = flat ? p.b * max_mb : p.b;
+  auto for_each_unit = [&](auto&& fn) {
+    for (int idx = tid; idx < n_idx; idx += TC5_SCHED_THREADS) {
+      const int s = flat ? idx / max_mb : idx;
+      const SeqInfo si(p, s);
+      if (!live(si.sq)) continue;
+      const int n = (si.sq + unit_rows - 1) / unit_rows;
+      if (flat) {
+        const int mb = idx - s * max_mb;
+        if (mb < n) fn(s, mb, si.sq, si.sk);
+        if (mb == max_mb - 1) for (int m2 = max_mb; m2 < n; m2++) fn(s, m2, si.sq, si.sk);
+      } else {
+        for (int mb = 0; mb < n; mb++) fn(s, mb, si.sq, si.sk);
+      }
+    }
+  };
+  for_each_unit([&](int, int mb, int sq, int sk) { atomicAdd(&bins[TC5_SCHED_BINS - 1 - cost_of(mb, sq, sk)], 1); });   // bin 0 = most expensive
   __syncthreads();
   // exclusive prefix sum over the 2048 bins (2 per thread)
   const int a = bins[2 * tid], b = bins[2 * tid + 1];
@@ -528,15 +577,10 @@ tc5_schedule_kernel(const __grid_constant__ KParams p, int2* items, int* header,
   bins[2 * tid] = excl; bins[2 * tid + 1] = excl + a;
   if (tid == TC5_SCHED_THREADS - 1) { header[0] = 0; header[1] = min(excl + v, max_items); }
   __syncthreads();
-  for (int s = tid; s < p.b; s += TC5_SCHED_THREADS) {
-    const SeqInfo si(p, s);
-    if (!live(si.sq)) continue;
-    const int n = (si.sq + unit_rows - 1) / unit_rows;
-    for (int mb = 0; mb < n; mb++) {
-      const int pos = atomicAdd(&bins[TC5_SCHED_BINS - 1 - cost_of(mb, si.sq, si.sk)], 1);
-      if (pos < max_items) items[pos] = make_int2(s, mb);
-    }
-  }
+  for_each_unit([&](int s, int mb, int sq, int sk) {
+    const int pos = atomicAdd(&bins[TC5_SCHED_BINS - 1 - cost_of(mb, sq, sk)], 1);
+    if (pos < max_items) items[pos] = make_int2(s, mb);
+  });
 }
 
 // =========================================================================================
