@@ -524,8 +524,9 @@ def bench_c4(fa, ext, dev, world, rank, pk, iters=20):
 def bench_c5(fa, ext, dev, world, rank, pk, batch, ctx=131072, iters=30):
     """C5 (BASELINE.json configs[4]): long-context decode, 32q/8kv D=128, ctx 131072, paged block 16,
     KV sequence split over the ranks (contiguous ctx/N keys per rank); per-rank (out fp32, lse) partials are
-    exchanged and LSE-combined (flash_fwd_kernel.h:1151-1221 lifted to ranks) by (a) ONE fused peer-memory
-    kernel (fa_b200_exchange_combine over NVLink) or (b) ONE NCCL all-gather + the combine kernel.
+    exchanged and LSE-combined (flash_fwd_kernel.h:1151-1221 lifted to ranks) (a) inside the decode kernel itself (ONE
+    launch per step: split merge + NVLink push + wait + combine), (b) by a separate peer-memory kernel
+    (fa_b200_exchange_combine) or (c) by ONE NCCL all-gather + the combine kernel.
     Strong scaling: t(1 GPU, whole sequence) is measured on rank 0 in the same run, eager and as a CUDA graph."""
     import torch
     import torch.distributed as dist
@@ -586,38 +587,48 @@ def bench_c5(fa, ext, dev, world, rank, pk, batch, ctx=131072, iters=30):
         return res
 
     # ---- sharded: (a) fused peer-memory exchange, (b) NCCL all-gather + combine ----
-    xch = sharded.PeerExchange(sharded.partial_record_numel(batch, 1, H, D), dev)
+    xch = sharded.PeerExchange.for_decode(batch, H, HK, D, dev)
+    f_one = lambda: sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
+                                                                 return_softmax_lse=True, exchange=xch, one_kernel=True)
     f_fused = lambda: sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
-                                                                   return_softmax_lse=True, exchange=xch)
+                                                                   return_softmax_lse=True, exchange=xch, one_kernel=False)
     f_nccl = lambda: sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
                                                                   return_softmax_lse=True)
+    oo, lo = f_one()
+    launches_one = ext.last_call_info.get("launches")
     of, lf = f_fused()
     on, ln = f_nccl()
     splits_n = ext.last_call_info.get("num_splits")
     torch.cuda.synchronize()
     par = None
     if rank == 0:
-        par = {"fused_out": (of.float() - o1.float()).abs().max().item(), "fused_lse": (lf - l1).abs().max().item(),
+        par = {"one_kernel_out": (oo.float() - o1.float()).abs().max().item(), "one_kernel_lse": (lo - l1).abs().max().item(),
+               "fused_out": (of.float() - o1.float()).abs().max().item(), "fused_lse": (lf - l1).abs().max().item(),
                "nccl_out": (on.float() - o1.float()).abs().max().item(), "nccl_lse": (ln - l1).abs().max().item()}
+    t_o = _timed(f_one, iters, world, dev)
+    t_og = _timed_graph(f_one, iters, world, dev)
     t_f = _timed(f_fused, iters, world, dev)
     t_n = _timed(f_nccl, iters, world, dev)
     t_fg = _timed_graph(f_fused, iters, world, dev)
     t_ng = _timed_graph(f_nccl, iters, world, dev)
     lens_local = sharded.seq_shard_lengths(lens, s, e)
     t_loc = _timed_graph(lambda: sharded.kvcache_partial(q, kc, vc, lens_local, bt), iters, world, dev)
-    best = min(x for x in (t_f, t_n, t_fg, t_ng) if x)
+    best = min(x for x in (t_o, t_og, t_f, t_n, t_fg, t_ng) if x)
     t1_best = min(x for x in (t1, t1g) if x)
     res.update({
+        "ms_one_kernel": t_o, "ms_one_kernel_cuda_graph": t_og, "launches_one_kernel": launches_one,
         "ms_fused_exchange": t_f, "ms_nccl_allgather": t_n, "ms_fused_exchange_cuda_graph": t_fg, "ms_nccl_allgather_cuda_graph": t_ng,
         "ms_local_split_decode_only_cuda_graph": t_loc, "num_splits_per_rank": splits_n,
         "ms": best, "speedup_vs_1gpu": t1_best / best, "strong_scaling_efficiency": t1_best / (world * best),
         "gbs_per_gpu": nbytes / world / (best * 1e-3) / 1e9, "frac_of_hbm_peak_per_gpu": nbytes / world / (best * 1e-3) / 1e9 / pk["hbm_gbs"],
         "gbs_per_gpu_local_kernel_only": (nbytes / world / (t_loc * 1e-3) / 1e9) if t_loc else None,
         "exchange_bytes_per_rank": sharded.partial_record_numel(batch, 1, H, D) * 4 * (world - 1),
-        "collective": "fa_b200_exchange_combine (peer-memory stores over NVLink, one kernel) | NCCL all_gather_into_tensor + fa_b200_combine",
+        "collective": "one_kernel: fa_decode_kernel merges its splits, pushes to the peers over NVLink, waits and combines (1 launch) | "
+                      "fused_exchange: decode + fa_b200_exchange_combine (2 launches) | nccl: decode + all_gather_into_tensor + fa_b200_combine",
         "parity_max_abs_vs_1gpu": par,
         # bf16 output of two different split trees (ranks x splits vs splits): one bf16 ulp at |o| < 4
-        "parity_ok": (max(par["fused_out"], par["nccl_out"]) <= 2e-2 and max(par["fused_lse"], par["nccl_lse"]) <= 1e-3) if rank == 0 else None})
+        "parity_ok": (max(par["one_kernel_out"], par["fused_out"], par["nccl_out"]) <= 2e-2 and
+                      max(par["one_kernel_lse"], par["fused_lse"], par["nccl_lse"]) <= 1e-3) if rank == 0 else None})
     del xch
     return res
 

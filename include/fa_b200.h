@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define FA_B200_ABI_VERSION 4
+#define FA_B200_ABI_VERSION 5
 
 enum {
   FA_OK = 0,
@@ -47,6 +47,30 @@ enum {
   FA_KERNEL_TILE = 2,        /* mma.sync 64-row tile kernel (all features) */
   FA_KERNEL_DECODE = 3       /* GQA-packed paged split-KV decode kernel */
 };
+
+/* Sequence-sharded decode in ONE kernel per rank (fwd_kvcache with FaFwdParams.fused_exchange set): the decode
+ * kernel's last CTA per (sequence, kv head) "unit" merges the unit's split-KV partials, pushes the merged fp32 rows
+ * into every rank's receive area through peer-mapped pointers (NVLink stores), publishes the unit's call number,
+ * waits for the peers' and writes the final (out, lse) — no separate combine or exchange launch, no NCCL call.  No
+ * reference analogue (the reference has no multi-GPU path); the algebra is combine_attn_seqk_parallel's
+ * (flash_fwd_kernel.h:1151-1221) applied to splits, then to ranks.  All areas live in one symmetric allocation per
+ * rank, zeroed once, mapped into every process of the box (e.g. torch symmetric memory):
+ *   recv  [2][world][max_units][unit_elems] fp32   receive area, double-buffered by the unit's call parity
+ *   flags [world][max_units] uint32                flags[r][u] = call number of unit u last delivered by rank r
+ *   state [max_units] uint32                       this rank's per-unit call numbers
+ *   split_counters [max_units] int32               arrival counters of the in-kernel split merge (self-resetting)
+ * Every rank must make the same sequence of calls (same b, h_k per call).  Slots are private to a unit, so the
+ * batch size may change from call to call. */
+#define FA_MAX_PEERS 8
+typedef struct FaFusedExchange {
+  void* recv[FA_MAX_PEERS];      /* rank r's receive area as mapped into THIS process */
+  uint32_t* flags[FA_MAX_PEERS]; /* rank r's flag array as mapped into THIS process */
+  uint32_t* state;               /* own */
+  int32_t* split_counters;       /* own */
+  int32_t rank, world;           /* world <= FA_MAX_PEERS */
+  int32_t max_units;             /* capacity: b*h_k of a call must not exceed it */
+  int64_t unit_elems;            /* fp32 per slot: >= seqlen_q*(h/h_k)*(d+1), multiple of 4 */
+} FaFusedExchange;
 
 typedef struct FaFwdParams {
   /* ---- tensors (device pointers), strides in elements ---- */
@@ -116,6 +140,18 @@ typedef struct FaFwdParams {
   int32_t force_kernel;  /* 0 = auto, else FA_KERNEL_* (tests) */
   int32_t kernel_used;   /* out */
   int32_t launches;      /* out: kernels launched by this call */
+
+  /* in: 1 = the caller guarantees that the first FA_B200_WS_HEAD_BYTES of `workspace` were zero when the buffer was
+   * first handed to this library and that nothing but this library has written there since (e.g. it was allocated
+   * zeroed and is used only as this library's workspace).  That region holds the arrival counters of the decode
+   * kernel's in-kernel split merge, which the kernel leaves at zero; with 0 the library clears them itself with a
+   * cudaMemsetAsync on every splitting call. */
+  int32_t workspace_clean;
+
+  /* ---- fwd_kvcache, sequence-sharded decode in one kernel (see FaFusedExchange); NULL = off.  Needs kv_shard_len > 0,
+   * a decode-shaped call (seqlen_q*(h/h_k) <= 32, 16 above d = 128), no ALiBi, no partial_out; o / softmax_lse
+   * receive the FINAL result on every rank. */
+  const FaFusedExchange* fused_exchange;
 } FaFwdParams;
 
 /* ABI version of the loaded library (== FA_B200_ABI_VERSION). */
@@ -130,6 +166,9 @@ const char* fa_b200_last_error(void);
 int fa_b200_num_splits_heuristic(int batch_nheads_mblocks, int num_sms, int num_n_blocks,
                                  int max_splits);
 
+/* Layout of every workspace: [FA_B200_WS_HEAD_BYTES: split arrival counters, see workspace_clean][payload: split-KV
+ * partials or the prefill work list].  16-byte aligned. */
+#define FA_B200_WS_HEAD_BYTES 16384
 /* Bytes of split-KV workspace the call described by *p needs (0 if it will not split).
  * `op` is 0 = fwd, 1 = varlen_fwd, 2 = fwd_kvcache.  Resolves p->num_splits==0 with the
  * heuristic exactly as the launch will.  Returns (size_t)-1 on invalid arguments. */
@@ -179,7 +218,6 @@ int fa_b200_combine(const void* o_part, const float* lse_part, void* o, float* l
  * are rank r's receive area ([2][world][record_elems] fp32) and flag array ([world][FA_XCHG_CTAS] uint32,
  * zeroed once) as mapped into THIS process (e.g. torch symmetric memory buffer_ptrs); state is this rank's own
  * per-CTA call counters ([FA_XCHG_CTAS] uint32, zeroed once).  All ranks must make the same sequence of calls. */
-#define FA_MAX_PEERS 8
 #define FA_XCHG_CTAS 64
 typedef struct FaExchangeParams {
   void* recv[FA_MAX_PEERS];
@@ -196,6 +234,7 @@ typedef struct FaExchangeParams {
 } FaExchangeParams;
 int fa_b200_exchange_combine(const FaExchangeParams* p, void* stream);
 size_t fa_b200_exchange_params_size(void);
+size_t fa_b200_fused_exchange_size(void);   /* sizeof(FaFusedExchange) as compiled */
 
 #ifdef __cplusplus
 }

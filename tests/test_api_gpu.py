@@ -370,6 +370,62 @@ def test_fused_exchange_single_rank_protocol():
         assert bool((out[2] == 0).all())
 
 
+@pytest.mark.parametrize("d,h,hk", [(128, 8, 2), (64, 16, 2), (256, 8, 1)])
+def test_one_kernel_sharded_decode_single_rank(d, h, hk):
+    """fwd_kvcache(fused_exchange=...) with world = 1: the decode kernel merges its own splits (arrival ticket), runs the
+    push / flag / wait protocol against itself and writes the final result — ONE launch.  Batch size and split count
+    change from call to call through one PeerExchange (slots and call numbers are per (sequence, kv head) unit), an
+    empty sequence gives O = 0 / LSE = +inf, and the result equals the ordinary kvcache call's."""
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import sharded
+    ext = _ext()
+    torch.manual_seed(0)
+    dev, dt, page, ctx = torch.device("cuda", 0), torch.bfloat16, 16, 4096
+    xch = sharded.PeerExchange.for_decode(6, h, hk, d, dev)
+    for it, (b, splits) in enumerate([(1, 0), (6, 3), (1, 7), (3, 1), (6, 0), (2, 16), (1, 0), (1, 1)]):
+        nblk = b * ctx // page
+        kc = torch.randn(nblk, page, hk, d, device=dev, dtype=dt); vc = torch.randn_like(kc)
+        bt = torch.randperm(nblk, device=dev).to(torch.int32).view(b, -1).contiguous()
+        lens = torch.randint(1, ctx + 1, (b,), device=dev).to(torch.int32)
+        lens[0] = ctx
+        if b >= 3:
+            lens[2] = 0
+        q = torch.randn(b, 1, h, d, device=dev, dtype=dt)
+        ref, lref = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=lens, block_table=bt, causal=True, num_splits=splits,
+                                                return_softmax_lse=True)
+        out, lse = sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=0, shard_end=ctx, causal=True,
+                                                                num_splits=splits, return_softmax_lse=True, exchange=xch, one_kernel=True)
+        assert ext.last_call_info["launches"] == 1 and ext.last_call_info["kernel_used"] == 3, (it, ext.last_call_info)
+        assert not torch.isnan(out.float()).any()
+        assert (out.float() - ref.float()).abs().max().item() <= 4e-3, it
+        fin = torch.isfinite(lref)
+        assert (lse[fin] - lref[fin]).abs().max().item() < 1e-4 and bool((torch.isinf(lse) == torch.isinf(lref)).all()), it
+        if b >= 3:
+            assert bool((out[2] == 0).all()) and bool(torch.isinf(lse[2]).all() and (lse[2] > 0).all())
+
+
+def test_split_decode_merges_in_kernel():
+    """Split-KV decode through the ordinary API is one launch now (the last CTA of each (sequence, kv head) merges the
+    splits; the reference launches flash_fwd_splitkv_combine_kernel, flash_fwd_launch_template.h:131-155) and equals
+    the merge of the same partials by the separate combine entry point."""
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import sharded
+    ext = _ext()
+    torch.manual_seed(4)
+    dev, dt = "cuda", torch.bfloat16
+    q = torch.randn(2, 1, 32, 128, device=dev, dtype=dt)
+    kc = torch.randn(2, 20000, 8, 128, device=dev, dtype=dt); vc = torch.randn_like(kc)
+    cs = torch.tensor([19999, 5], dtype=torch.int32, device=dev)
+    out, lse = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=cs, return_softmax_lse=True)
+    assert ext.last_call_info["launches"] == 1 and ext.last_call_info["num_splits"] > 1
+    # the partial-result mode with the same split count, merged per split count 1 => the plain kernel result
+    one, lone = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=cs, num_splits=1, return_softmax_lse=True)
+    assert (out.float() - one.float()).abs().max().item() <= 4e-3 and (lse - lone).abs().max().item() < 1e-4
+    ref32, _ = orc.attention_ref(q, kc, vc, None, torch.arange(20000, device=dev).expand(2, 20000) < cs.view(-1, 1))
+    pt, _ = orc.attention_ref(q, kc, vc, None, torch.arange(20000, device=dev).expand(2, 20000) < cs.view(-1, 1), upcast=False, reorder_ops=True)
+    assert (out.float() - ref32.float()).abs().max().item() <= 3 * (pt.float() - ref32.float()).abs().max().item() + 1e-5
+
+
 def test_varlen_seqused_k():
     """varlen_fwd(seqused_k=...) (flash_api.cpp:428,:553-556; BlockInfo src/block_info.h:24): keys beyond
     seqused_k[b] are ignored although cu_seqlens_k spans them.  Prefill rows run on the tcgen05 kernel,

@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol():
 
 
 def test_params_layout_and_version():
-    assert lib.fa_b200_abi_version() == 4
+    assert lib.fa_b200_abi_version() == 5
     assert lib.fa_b200_params_size() == C.sizeof(FaFwdParams)
 
 
@@ -97,7 +97,7 @@ def test_workspace_matches_split_choice():
     P.num_splits = 0
     need = lib.fa_b200_workspace_bytes(C.byref(P), 2)
     s = lib.fa_b200_num_splits_heuristic(4, 296, 2, 128)
-    assert s == 2 and need == s * 2 * 8 * 1 * (128 + 1) * 4 + 16
+    assert s == 2 and need == 16384 + s * 2 * 8 * 1 * (128 + 1) * 4 + 16     # counter head + partials + slack
     P.num_splits = 1
     assert lib.fa_b200_workspace_bytes(C.byref(P), 2) == 0
     P.num_splits = 129

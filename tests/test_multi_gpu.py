@@ -1,6 +1,7 @@
 """GPU, 2 ranks (skipped with fewer than 2 devices; run with `gpurun --gpus 2`): the two shardings on real
 GPUs, one process per GPU over NCCL.
-* sequence-sharded decode through BOTH exchanges (fused peer-memory kernel / NCCL all-gather + combine) against
+* sequence-sharded decode through ALL THREE exchanges (one-kernel decode + exchange / separate peer-memory exchange
+  kernel / NCCL all-gather + combine) against
   the single-GPU kernel over the whole sequence, with the batch size ALTERNATING between calls through one
   PeerExchange — the continuous-batching pattern in which per-CTA protocol state could drift apart;
 * head-sharded mixed prefill+decode varlen batch against rank 0 running all heads.
@@ -37,7 +38,7 @@ def _worker(rank, world, port, ret):
         s, e = sharded.seq_shard_range(rank, world, ctx, page)
         e = min(e, ctx)
         L = e - s
-        xch = sharded.PeerExchange(sharded.partial_record_numel(8, 1, H, D), dev)
+        xch = sharded.PeerExchange.for_decode(8, H, HK, D, dev)
         for step, b in enumerate([1, 4, 1, 8, 3, 8, 1, 1, 5, 2, 8, 1]):
             g = torch.Generator(device="cpu").manual_seed(1000 + step)          # same data on every rank
             q = torch.randn(b, 1, H, D, generator=g).to(dt).to(dev)
@@ -51,16 +52,19 @@ def _worker(rank, world, port, ret):
             kc = torch.empty(nblk, page, HK, D, dtype=dt, device=dev); vc = torch.empty_like(kc)
             kc[bt.view(-1).long()] = kfull[:, s:e].reshape(nblk, page, HK, D).to(dev)
             vc[bt.view(-1).long()] = vfull[:, s:e].reshape(nblk, page, HK, D).to(dev)
+            oo, lo = sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
+                                                                  return_softmax_lse=True, exchange=xch, one_kernel=True)
             of, lf = sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
-                                                                  return_softmax_lse=True, exchange=xch)
+                                                                  return_softmax_lse=True, exchange=xch, one_kernel=False)
             on, ln = sharded.flash_attn_with_kvcache_seq_sharded(q, kc, vc, lens, bt, shard_start=s, shard_end=e, causal=True,
                                                                   return_softmax_lse=True)
             o1, l1 = fa.flash_attn_with_kvcache(q, kfull.to(dev), vfull.to(dev), cache_seqlens=lens, causal=True,
                                                 return_softmax_lse=True)
             torch.cuda.synchronize()
-            errs[f"seq{step}_b{b}"] = (max((of.float() - o1.float()).abs().max().item(), (on.float() - o1.float()).abs().max().item()),
-                                       max((lf - l1).abs().max().item(), (ln - l1).abs().max().item()),
-                                       (of.float() - on.float()).abs().max().item())
+            fin = torch.isfinite(l1)
+            errs[f"seq{step}_b{b}"] = (max((x.float() - o1.float()).abs().max().item() for x in (oo, of, on)),
+                                       max((x[fin] - l1[fin]).abs().max().item() for x in (lo, lf, ln)),
+                                       max((oo.float() - on.float()).abs().max().item(), (of.float() - on.float()).abs().max().item()))
         # ---------------- head-sharded mixed batch
         Hq = 16
         qs, ks = sharded.head_shard(rank, world, Hq, HK // 2)

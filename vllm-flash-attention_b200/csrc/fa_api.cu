@@ -108,7 +108,11 @@ struct Plan {
   bool is_bf16;
   int num_sms;
   int decode_rows;   // > 0: mixed varlen batch — sequences with at most this many packed rows go to the decode kernel
+  bool fused_tail;   // decode kernel merges its own splits (and exchanges across GPUs): no separate combine launch
+  size_t lse_floats, o_floats;   // split workspace payload: lse block (padded to 4 floats) | o block | [arrival counters]
+  bool counters_in_head;
 };
+static_assert(FA_MAX_PEERS == FA_KP_MAX_PEERS, "peer capacity of the C ABI and of KParams must agree");
 
 // Validation + normalisation shared by the three ops.  Mirrors the checks of mha_fwd /
 // mha_varlen_fwd / mha_fwd_kvcache that do not need tensor metadata beyond what FaFwdParams holds.
@@ -183,6 +187,26 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   k.window_left = wl; k.window_right = wr;
   k.is_local = (wl >= 0 || wr >= 0) && !k.is_causal;
 
+  // A KV shard knows its keys only by LOCAL position: masks and biases that depend on the global key index would be
+  // silently wrong, and without a partial result there is nothing to merge with the other shards.
+  if (a->kv_shard_len > 0) {
+    FA_CHECK(a->alibi_slopes == nullptr, "kv_shard: ALiBi is not supported (the bias depends on the global key position)");
+    FA_CHECK(a->seqlen_q == 1 || !(k.is_causal || k.is_local), "kv_shard: causal / local masks need seqlen_q == 1");
+    FA_CHECK(a->partial_out || a->fused_exchange, "kv_shard: needs partial_out or fused_exchange (a shard's result is a partial)");
+  }
+  const FaFusedExchange* fx = a->fused_exchange;
+  if (fx) {
+    FA_CHECK(op == OP_KVCACHE && a->kv_shard_len > 0 && !a->partial_out, "fused_exchange: fwd_kvcache with kv_shard_len > 0 and without partial_out only");
+    FA_CHECK(fx->world >= 1 && fx->world <= FA_MAX_PEERS && fx->rank >= 0 && fx->rank < fx->world, "fused_exchange: bad rank/world");
+    FA_CHECK(fx->state && fx->split_counters, "fused_exchange: NULL state / split_counters");
+    for (int r = 0; r < fx->world; r++)
+      FA_CHECK(fx->recv[r] && fx->flags[r] && (reinterpret_cast<uintptr_t>(fx->recv[r]) & 15) == 0, "fused_exchange: recv/flags pointer missing or misaligned");
+    FA_CHECK((int64_t)a->b * a->h_k <= fx->max_units, "fused_exchange: b*h_k = %lld exceeds max_units = %d", (long long)a->b * a->h_k, fx->max_units);
+    FA_CHECK(fx->unit_elems % 4 == 0 && fx->unit_elems >= (int64_t)a->seqlen_q * k.group * (a->d + 1),
+             "fused_exchange: unit_elems too small for seqlen_q*group*(d+1) or not a multiple of 4");
+    FA_CHECK(a->softmax_lse != nullptr, "fused_exchange needs softmax_lse");
+  }
+
   pl->is_bf16 = a->is_bf16 != 0;
   const int num_sms = a->num_sms > 0 ? a->num_sms : device_sms();
 
@@ -201,6 +225,7 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
       if (op == OP_VARLEN && decode_supported(a->d, k.group)) pl->decode_rows = a->d <= 128 ? 32 : 16;   // the decode kernel's row capacity
     } else kernel = FA_KERNEL_TILE;
   }
+  if (fx) FA_CHECK(kernel == FA_KERNEL_DECODE, "fused_exchange: the call must have a decode shape (seqlen_q*(h/h_k) <= 32; 16 above d = 128)");
   if (kernel == FA_KERNEL_DECODE) FA_CHECK(decode_supported(a->d, rows), "decode kernel: d/rows not supported");
   if (kernel == FA_KERNEL_TC5_PREFILL) FA_CHECK(!k.partial && (tc5_supported(k) || as_single_page(a, op, &k)), "tcgen05 prefill kernel: shape/layout not supported");
   if (kernel == FA_KERNEL_TILE) FA_CHECK(tile_supported(a->d), "head dimension must be a multiple of 32 (reference build: -DFLASHATTENTION_DISABLE_UNEVEN_K)");
@@ -227,10 +252,20 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   }
   k.num_splits = pl->num_splits = splits;
   pl->num_sms = num_sms;
-  pl->ws_bytes = splits > 1 ? (size_t)splits * a->b * a->h * std::max(a->seqlen_q, 1) * (a->d + 1) * sizeof(float) : 0;
+  // split workspace: lse block, padded to 4 floats so that the o block stays 16-byte aligned | o block | the arrival
+  // counters of the decode kernel's in-kernel merge (when they are not part of a fused_exchange allocation)
+  const size_t part_rows = (size_t)splits * a->b * a->h * std::max(a->seqlen_q, 1);
+  pl->lse_floats = (part_rows + 3) / 4 * 4;
+  pl->o_floats = part_rows * a->d;
+  pl->fused_tail = kernel == FA_KERNEL_DECODE && (splits > 1 || fx != nullptr);
+  // arrival counters: in the workspace head (kept at zero between calls: workspace_clean) when they fit, else behind the partials
+  pl->counters_in_head = (size_t)a->b * a->h_k * sizeof(int) <= FA_B200_WS_HEAD_BYTES;
+  pl->ws_bytes = splits > 1 ? FA_B200_WS_HEAD_BYTES + (pl->lse_floats + pl->o_floats) * sizeof(float) +
+                              ((pl->fused_tail && !fx && !pl->counters_in_head) ? (size_t)a->b * a->h_k * sizeof(int) : 0) : 0;
   if (kernel == FA_KERNEL_TC5_PREFILL) {
     if (op == OP_VARLEN) FA_CHECK(a->total_q > 0, "total_q (rows of q) must be given for varlen_fwd");
     pl->ws_bytes = tc5_workspace_bytes(k, a->total_q, num_sms);    // cost-sorted work list of the persistent kernel
+    if (pl->ws_bytes) pl->ws_bytes += FA_B200_WS_HEAD_BYTES;
   }
   return FA_OK;
 }
@@ -247,11 +282,22 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
   if (pl.num_splits > 1) {
     if (a->workspace == nullptr || a->workspace_bytes < pl.ws_bytes)
       return fail(FA_ERR_WORKSPACE, "split-KV workspace too small: need %zu bytes, got %zu", pl.ws_bytes, a->workspace_bytes);
-    const size_t rows = (size_t)a->b * a->h * a->seqlen_q;
-    k.lse_accum = reinterpret_cast<float*>(a->workspace);
-    k.o_accum = k.lse_accum + (size_t)pl.num_splits * rows;
-    if ((reinterpret_cast<uintptr_t>(k.o_accum) & 15) != 0)   // keep float4 alignment
-      k.o_accum = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(k.o_accum) + 15) & ~(uintptr_t)15);
+    if ((reinterpret_cast<uintptr_t>(a->workspace) & 15) != 0) return fail(FA_ERR_INVALID, "workspace must be 16-byte aligned");
+    k.lse_accum = reinterpret_cast<float*>(reinterpret_cast<char*>(a->workspace) + FA_B200_WS_HEAD_BYTES);
+    k.o_accum = k.lse_accum + pl.lse_floats;
+    if (pl.fused_tail && !a->fused_exchange) {
+      k.split_counters = pl.counters_in_head ? reinterpret_cast<int*>(a->workspace) : reinterpret_cast<int*>(k.o_accum + pl.o_floats);
+      if (!(a->workspace_clean && pl.counters_in_head)) {
+        cudaError_t em = cudaMemsetAsync(k.split_counters, 0, (size_t)a->b * a->h_k * sizeof(int), stream);   // a memset node, not a kernel
+        if (em != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error clearing the split arrival counters: %s", cudaGetErrorString(em));
+      }
+    }
+  }
+  if (const FaFusedExchange* fx = a->fused_exchange) {
+    for (int r = 0; r < fx->world; r++) { k.xchg_recv[r] = reinterpret_cast<float*>(fx->recv[r]); k.xchg_flags[r] = fx->flags[r]; }
+    k.xchg_state = fx->state; k.xchg_rank = fx->rank; k.xchg_world = fx->world;
+    k.xchg_max_units = fx->max_units; k.xchg_unit_elems = fx->unit_elems;
+    k.split_counters = fx->split_counters;                 // zeroed once by the owner, reset by the kernel
   }
   if (k.partial && pl.num_splits == 1) {   // the single "split" IS the result: (b,h,sq,d) fp32 + lse
     k.o_accum = reinterpret_cast<float*>(a->o);
@@ -266,8 +312,8 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
         if (a->workspace == nullptr || a->workspace_bytes < pl.ws_bytes)
           return fail(FA_ERR_WORKSPACE, "work-list workspace too small: need %zu bytes, got %zu", pl.ws_bytes, a->workspace_bytes);
         if ((reinterpret_cast<uintptr_t>(a->workspace) & 7) != 0) return fail(FA_ERR_INVALID, "workspace must be 8-byte aligned");
-        k.work_header = reinterpret_cast<int*>(a->workspace);
-        k.work_items = reinterpret_cast<int2*>(reinterpret_cast<char*>(a->workspace) + 16);
+        k.work_header = reinterpret_cast<int*>(reinterpret_cast<char*>(a->workspace) + FA_B200_WS_HEAD_BYTES);
+        k.work_items = reinterpret_cast<int2*>(reinterpret_cast<char*>(a->workspace) + FA_B200_WS_HEAD_BYTES + 16);
       }
       a->launches = pl.ws_bytes ? 1 : 0;
       // ---- decode half of a mixed batch: forked onto a side stream, ahead of the prefill launches.  A batch
@@ -310,7 +356,7 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
   }
   if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in attention kernel launch: %s", cudaGetErrorString(e));
   a->launches += 1;
-  if (pl.num_splits > 1) {
+  if (pl.num_splits > 1 && !pl.fused_tail) {
     CombineParams c;
     c.o_part = k.o_accum; c.lse_part = k.lse_accum; c.o = a->o; c.lse = a->softmax_lse;
     c.n_splits = pl.num_splits; c.b = a->b; c.h = a->h; c.sq = a->seqlen_q; c.d = a->d;
@@ -441,6 +487,7 @@ extern "C" int fa_b200_exchange_combine(const FaExchangeParams* a, void* stream)
   return FA_OK;
 }
 extern "C" size_t fa_b200_exchange_params_size(void) { return sizeof(FaExchangeParams); }
+extern "C" size_t fa_b200_fused_exchange_size(void) { return sizeof(FaFusedExchange); }
 
 // ---------------------------------------------------------------------------------------------
 // fa_b200_fwd_kvcache_static_scratch — fwd_kvcache for callers that cannot allocate (CUDA-graph
@@ -452,9 +499,11 @@ extern "C" size_t fa_b200_exchange_params_size(void) { return sizeof(FaExchangeP
 //     A call whose plan needs more is rejected (FA_ERR_WORKSPACE) before anything is launched.
 //   * The array's NAME is only a host-side stand-in in host code: its device address is fetched with
 //     cudaGetSymbolAddress once per device (that device current) and that pointer goes to the kernels.
-//   * Every call shares the array and finds the previous call's contents in it.  Nothing has to start
-//     at zero: every CTA of the split kernel writes its (split, row) slice, empty splits included
-//     (O = 0, lse = -inf), before the combine kernel of the same call reads it, and the prefill work
+//   * Every call shares the array and finds the previous call's contents in it.  What has to start at
+//     zero are the arrival counters of the in-kernel split merge (workspace head): the array is zero when
+//     the module loads and the kernel's last CTA per unit puts its counter back to zero.  The partials
+//     need no clearing: every CTA of the split kernel writes its (split, row) slice, empty splits included
+//     (O = 0, lse = -inf), before the unit's last CTA reads them, and the prefill work
 //     list (when a many-row call lands on the tcgen05 kernel) is rebuilt by tc5_schedule_kernel, which
 //     also resets its draw counter.  Calls that OVERLAP on the GPU (different streams, or graphs
 //     replayed concurrently) race on the array: serialise them, or use fa_b200_fwd_kvcache with
@@ -499,7 +548,9 @@ extern "C" int fa_b200_fwd_kvcache_static_scratch(FaFwdParams* a, void* stream) 
   }
   a->workspace = ptr;
   a->workspace_bytes = need ? (size_t)FA_B200_STATIC_SCRATCH_BYTES : 0;
+  const int clean_in = a->workspace_clean;
+  a->workspace_clean = 1;      // the static array is zero when the module loads and the arrival counters reset themselves
   rc = run_plan(a, OP_KVCACHE, stream);
-  a->workspace = nullptr; a->workspace_bytes = 0;              // the caller's block stays as it was passed
+  a->workspace = nullptr; a->workspace_bytes = 0; a->workspace_clean = clean_in;   // the caller's block stays as it was passed
   return rc;
 }

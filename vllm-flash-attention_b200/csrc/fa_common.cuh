@@ -41,7 +41,15 @@ struct KParams {
   int single_page;                              // tcgen05 prefill over a NON-paged cache: each cache entry is one page of seqlen_k rows,
                                                 // block_table (if any) is cache_batch_idx with one column, else block = sequence index
   int partial;                                  // write fp32 partials (o_accum/lse_accum, -inf for empty rows) even with 1 split
+  // ---- decode kernel: in-kernel split merge and cross-GPU exchange (fa_decode.cu, "fused tail") ----
+  int* split_counters;                          // [b*h_k] arrival counters, zero before the launch, reset by the kernel; NULL: the
+                                                // split partials are merged by a separate fa_combine_kernel launch
+  float* xchg_recv[8]; unsigned* xchg_flags[8]; // sequence-sharded decode in ONE kernel: peer-mapped receive areas / flag arrays
+  unsigned* xchg_state;                         // this rank's per-unit call numbers
+  int xchg_rank, xchg_world, xchg_max_units;    // xchg_world == 0: no exchange
+  int64_t xchg_unit_elems;                      // fp32 per (parity, source rank, unit) slot
 };
+constexpr int FA_KP_MAX_PEERS = 8;
 
 // Per-sequence geometry — the analogue of BlockInfo (reference src/block_info.h:11-42).
 struct SeqInfo {
@@ -102,6 +110,29 @@ __device__ __forceinline__ float fast_exp2(float x) {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+// system-scope flag traffic of the cross-GPU exchanges (peer-mapped memory over NVLink)
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+#ifndef FA_XCHG_TIMEOUT_NS
+#define FA_XCHG_TIMEOUT_NS 120000000000ll   /* a peer may be late by a module load, a graph capture or a host stall; a MISSING peer still ends in a launch failure, not a hung GPU */
+#endif
+// wait until *flag has reached call number n (wrap-safe); bounded
+__device__ __forceinline__ void wait_flag_sys(const unsigned* flag, unsigned n) {
+  long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  while ((int)(ld_acquire_sys(flag) - n) < 0) {
+    long long t1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    if (t1 - t0 > FA_XCHG_TIMEOUT_NS) __trap();
+  }
 }
 
 // ---------------------------------------------------------------------------------------

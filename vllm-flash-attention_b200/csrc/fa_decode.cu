@@ -30,7 +30,8 @@ struct DecodeCfg {
   static constexpr int RED_STRIDE = D + 8;                      // floats
   static constexpr int RED_BYTES = ROWS * RED_STRIDE * 4;
   static constexpr int STAT_BYTES = (2 * NW + 2) * ROWS * 4;    // m[NW][ROWS], l[NW][ROWS], inv_l, lse
-  static constexpr int MAIN_BYTES = RING_BYTES > RED_BYTES ? RING_BYTES : RED_BYTES;
+  static constexpr int MERGE_BYTES = RED_BYTES + ROWS * 128 * 4;   // fused tail: O rows + the (row, split) weights of up to 128 splits
+  static constexpr int MAIN_BYTES = RING_BYTES > MERGE_BYTES ? RING_BYTES : MERGE_BYTES;
   static constexpr int SMEM = Q_BYTES + MAIN_BYTES + STAT_BYTES;
 };
 
@@ -214,7 +215,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
         const bool empty = !(lt > 0.f);
         row_inv[row] = empty ? 0.f : 1.f / lt;
         // natural-log LSE = max*scale + ln(sum) (softmax.h:179); m is in log2 units
-        row_lse[row] = empty ? ((p.num_splits > 1 || p.partial) ? -INFINITY : INFINITY)
+        row_lse[row] = empty ? ((p.num_splits > 1 || p.partial || p.split_counters != nullptr || p.xchg_world > 0) ? -INFINITY : INFINITY)
                              : mt * 0.6931471805599453f + __logf(lt);
       }
     }
@@ -239,6 +240,213 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
 
   // ---- write out ----
   const int Rw = min(R, ROWS);
+  if (p.split_counters != nullptr || p.xchg_world > 0) {
+    // ================= fused tail: split merge (+ cross-GPU exchange) inside this kernel =================
+    // Replaces the separate fa_combine_kernel launch (combine_attn_seqk_parallel, flash_fwd_kernel.h:1092-1250) and,
+    // for sequence-sharded decode, the separate exchange kernel: the LAST CTA to finish a (sequence, kv head) unit
+    // merges the unit's split partials, and — sharded — pushes the merged rows to every rank over NVLink, waits
+    // for the peers' rows of the same unit and writes the final result.  Per-unit state only: no CTA waits for
+    // another CTA of this grid, so nothing has to be co-resident.
+    __shared__ int s_last;
+    __shared__ unsigned s_n;
+    const int tid = threadIdx.x;
+    const int unit = bidb * p.h_k + kvh;
+    auto head_of = [&](int r, int& qpos) { qpos = r / g; return kvh * g + (r - qpos * g); };
+    if (p.num_splits > 1) {
+      // a. this split's partial, fp32 (split, b, h, sq[, d]) — the layout of the reference's accum buffers
+      for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
+        const int r = idx / (D / 4), c4 = idx % (D / 4);
+        int qpos; const int hd = head_of(r, qpos);
+        const int64_t orow = (((int64_t)split * p.b + bidb) * p.h + hd) * p.lse_seq_stride + qpos;
+        const float inv = row_inv[r];
+        float4 x = *reinterpret_cast<const float4*>(red + r * Cfg::RED_STRIDE + c4 * 4);
+        x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
+        *reinterpret_cast<float4*>(p.o_accum + orow * D + c4 * 4) = x;
+      }
+      for (int r = tid; r < Rw; r += NW * 32) {
+        int qpos; const int hd = head_of(r, qpos);
+        p.lse_accum[(((int64_t)split * p.b + bidb) * p.h + hd) * p.lse_seq_stride + qpos] = row_lse[r];
+      }
+      // b. arrival ticket: the last CTA of the unit carries on, the others are done
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) {
+        const int t = atomicAdd(p.split_counters + unit, 1);
+        s_last = t == p.num_splits - 1;
+        if (s_last) p.split_counters[unit] = 0;          // ready for the next launch
+      }
+      __syncthreads();
+      if (!s_last) return;
+      __threadfence();
+      // c. merge the unit's splits into red / row_lse.  First the weights exp(lse_s - lse) of every (row, split) into
+      // shared memory (one warp per row, lanes own splits); then every thread owns (row, 4-column) items and streams the
+      // splits with 8 independent 16-byte loads in flight — the partials sit in L2, and a walk with one or two loads in
+      // flight per lane is what made this tail cost more than the streaming loop of a short split.  Fixed order:
+      // deterministic.
+      const int S = p.num_splits;
+      const int64_t sstride = (int64_t)p.b * p.h * p.lse_seq_stride;
+      float* wsm = red + ROWS * Cfg::RED_STRIDE;            // [Rw][S] weights, behind the O rows (the ring is free by now)
+      for (int r = warp; r < Rw; r += NW) {
+        int qpos; const int hd = head_of(r, qpos);
+        const int64_t row0 = ((int64_t)bidb * p.h + hd) * p.lse_seq_stride + qpos;
+        float ls[4], mx = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const int s2 = lane + 32 * i;
+          ls[i] = s2 < S ? __ldcg(p.lse_accum + s2 * sstride + row0) : -INFINITY;
+          mx = fmaxf(mx, ls[i]);
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+        const float mx_safe = mx == -INFINITY ? 0.f : mx;
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; i++) sum += expf(ls[i] - mx_safe);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+        const bool empty = !(sum > 0.f);
+        const float lse = empty ? -INFINITY : logf(sum) + mx_safe;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+          const int s2 = lane + 32 * i;
+          if (s2 < S) wsm[r * S + s2] = empty ? 0.f : expf(ls[i] - lse);
+        }
+        if (lane == 0) row_lse[r] = lse;
+      }
+      __syncthreads();
+      for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
+        const int r = idx / (D / 4), c4 = idx % (D / 4);
+        int qpos; const int hd = head_of(r, qpos);
+        const float* src = p.o_accum + (((int64_t)bidb * p.h + hd) * p.lse_seq_stride + qpos) * D + c4 * 4;
+        const float* wr = wsm + r * S;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        int s2 = 0;
+        for (; s2 + 8 <= S; s2 += 8) {
+          float4 x[8];
+#pragma unroll
+          for (int u = 0; u < 8; u++) x[u] = __ldcg(reinterpret_cast<const float4*>(src + (s2 + u) * sstride * D));
+#pragma unroll
+          for (int u = 0; u < 8; u++) {
+            const float w = wr[s2 + u];
+            acc.x += w * x[u].x; acc.y += w * x[u].y; acc.z += w * x[u].z; acc.w += w * x[u].w;
+          }
+        }
+        for (; s2 < S; s2++) {
+          const float4 x = __ldcg(reinterpret_cast<const float4*>(src + s2 * sstride * D));
+          const float w = wr[s2];
+          acc.x += w * x.x; acc.y += w * x.y; acc.z += w * x.z; acc.w += w * x.w;
+        }
+        *reinterpret_cast<float4*>(red + r * Cfg::RED_STRIDE + c4 * 4) = acc;
+      }
+      __syncthreads();
+    } else {
+      // one split: this CTA's own result is the unit's; normalise it in place (row_lse already holds -inf for empty rows)
+      for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
+        const int r = idx / (D / 4), c4 = idx % (D / 4);
+        const float inv = row_inv[r];
+        float4 x = *reinterpret_cast<const float4*>(red + r * Cfg::RED_STRIDE + c4 * 4);
+        x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
+        *reinterpret_cast<float4*>(red + r * Cfg::RED_STRIDE + c4 * 4) = x;
+      }
+      __syncthreads();
+    }
+    // red[r][0..D) = this rank's normalised fp32 O rows of the unit, row_lse[r] = natural-log LSE (-inf: no key)
+
+    if (p.xchg_world > 0) {
+      // d. exchange (see fa_exchange.cu for the two-kernel form of the same protocol): call number n of THIS unit;
+      // slot (n & 1, source rank, unit) of every rank's receive area is private to the unit, so units whose call
+      // numbers differ (varying batch sizes) never touch each other's data; a rank cannot run two calls ahead of a
+      // peer for the same unit (its call n+1 needs the peer's flag n+1, sent after the peer finished call n).
+      if (tid == 0) s_n = p.xchg_state[unit] + 1u;
+      __syncthreads();
+      const unsigned n = s_n;
+      const int W = p.xchg_world;
+      auto slot = [&](int src) { return ((int64_t)((n & 1u) * W + src) * p.xchg_max_units + unit) * p.xchg_unit_elems; };
+      const int64_t mine = slot(p.xchg_rank);
+      for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
+        const int r = idx / (D / 4), c4 = idx % (D / 4);
+        const float4 x = *reinterpret_cast<const float4*>(red + r * Cfg::RED_STRIDE + c4 * 4);
+        for (int w = 0; w < W; w++) *reinterpret_cast<float4*>(p.xchg_recv[w] + mine + r * D + c4 * 4) = x;
+      }
+      for (int r = tid; r < Rw; r += NW * 32) {
+        const float l = row_lse[r];
+        for (int w = 0; w < W; w++) p.xchg_recv[w][mine + Rw * D + r] = l;
+      }
+      __threadfence_system();
+      __syncthreads();
+      if (tid < W) {
+        st_release_sys(p.xchg_flags[tid] + p.xchg_rank * p.xchg_max_units + unit, n);
+        wait_flag_sys(p.xchg_flags[p.xchg_rank] + tid * p.xchg_max_units + unit, n);
+      }
+      if (tid == 0) p.xchg_state[unit] = n;
+      __syncthreads();
+      // e. merge the ranks' rows: one warp per row
+      const float* base = p.xchg_recv[p.xchg_rank];
+      for (int r = warp; r < Rw; r += NW) {
+        float ls[FA_KP_MAX_PEERS], mx = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < FA_KP_MAX_PEERS; w++) {
+          ls[w] = w < W ? __ldcg(base + slot(w) + Rw * D + r) : -INFINITY;
+          mx = fmaxf(mx, ls[w]);
+        }
+        const bool empty = mx == -INFINITY;
+        float sum = 0.f;
+#pragma unroll
+        for (int w = 0; w < FA_KP_MAX_PEERS; w++) sum += empty ? 0.f : expf(ls[w] - mx);
+        const float lse = empty ? -INFINITY : logf(sum) + mx;
+        float wg[FA_KP_MAX_PEERS];
+#pragma unroll
+        for (int w = 0; w < FA_KP_MAX_PEERS; w++) wg[w] = empty ? 0.f : expf(ls[w] - lse);
+        for (int col = lane * 4; col < D; col += 128) {
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int w = 0; w < FA_KP_MAX_PEERS; w++) {
+            if (w < W) {
+              const float4 x = __ldcg(reinterpret_cast<const float4*>(base + slot(w) + r * D + col));
+              acc.x += wg[w] * x.x; acc.y += wg[w] * x.y; acc.z += wg[w] * x.z; acc.w += wg[w] * x.w;
+            }
+          }
+          *reinterpret_cast<float4*>(red + r * Cfg::RED_STRIDE + col) = acc;
+        }
+        if (lane == 0) row_lse[r] = lse;
+      }
+      __syncthreads();
+    }
+
+    // f. final rows: fp32 record (partial-result mode) or the output dtype; LSE +inf for rows without any key
+    if (p.partial) {
+      for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
+        const int r = idx / (D / 4), c4 = idx % (D / 4);
+        int qpos; const int hd = head_of(r, qpos);
+        const int64_t orow = ((int64_t)bidb * p.h + hd) * p.lse_seq_stride + qpos;
+        *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.o) + orow * D + c4 * 4) = *reinterpret_cast<const float4*>(red + r * Cfg::RED_STRIDE + c4 * 4);
+      }
+      for (int r = tid; r < Rw; r += NW * 32) {
+        int qpos; const int hd = head_of(r, qpos);
+        p.lse[((int64_t)bidb * p.h + hd) * p.lse_seq_stride + qpos] = row_lse[r];
+      }
+    } else {
+      T* ob = reinterpret_cast<T*>(p.o) + o_seq_offset(p, bidb);
+      for (int idx = tid; idx < Rw * CPR; idx += NW * 32) {
+        const int r = idx / CPR, c = idx % CPR;
+        int qpos; const int hd = head_of(r, qpos);
+        const float* src = red + r * Cfg::RED_STRIDE + c * 8;
+        const float4 a = *reinterpret_cast<const float4*>(src), b2 = *reinterpret_cast<const float4*>(src + 4);
+        uint4 pk;
+        pk.x = Pack2<T>::pack(a.x, a.y); pk.y = Pack2<T>::pack(a.z, a.w);
+        pk.z = Pack2<T>::pack(b2.x, b2.y); pk.w = Pack2<T>::pack(b2.z, b2.w);
+        *reinterpret_cast<uint4*>(ob + (int64_t)qpos * p.o_row_stride + (int64_t)hd * p.o_head_stride + c * 8) = pk;
+      }
+      if (p.lse) {
+        for (int r = tid; r < Rw; r += NW * 32) {
+          int qpos; const int hd = head_of(r, qpos);
+          const float l = row_lse[r];
+          p.lse[((int64_t)bidb * p.h + hd) * p.lse_seq_stride + qpos] = l == -INFINITY ? INFINITY : l;
+        }
+      }
+    }
+    return;
+  }
   if ((p.num_splits > 1 || p.partial)) {
     // fp32 partials, (split, b, h, sq[, d]) like the reference's accum buffers (flash_api.cpp:212-213)
     for (int idx = threadIdx.x; idx < Rw * (D / 4); idx += NW * 32) {

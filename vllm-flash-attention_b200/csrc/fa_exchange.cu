@@ -23,10 +23,6 @@
 #include "fa_common.cuh"
 #include "fa_launch.h"
 
-#ifndef FA_XCHG_TIMEOUT_NS
-#define FA_XCHG_TIMEOUT_NS 120000000000ll   /* a peer may be late by a module load, a graph capture or a host stall; a MISSING peer still ends in a launch failure, not a hung GPU */
-#endif
-
 namespace fa {
 
 struct ExchangeParams {
@@ -41,15 +37,6 @@ struct ExchangeParams {
   int64_t o_batch_stride, o_row_stride, o_head_stride;
   int out_dtype;            // 0 fp32, 1 bf16, 2 fp16
 };
-
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 
 __global__ void __launch_bounds__(256) fa_exchange_combine_kernel(const __grid_constant__ ExchangeParams p) {
   __shared__ unsigned s_n;
@@ -78,13 +65,7 @@ __global__ void __launch_bounds__(256) fa_exchange_combine_kernel(const __grid_c
     const int r = threadIdx.x;
     st_release_sys(p.flags[r] + p.rank * FA_XCHG_CTAS + cta, n);
     // ---- 2. wait for rank r's slice of call n ----
-    long long t0;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    while ((int)(ld_acquire_sys(p.flags[p.rank] + r * FA_XCHG_CTAS + cta) - n) < 0) {
-      long long t1;
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-      if (t1 - t0 > FA_XCHG_TIMEOUT_NS) __trap();
-    }
+    wait_flag_sys(p.flags[p.rank] + r * FA_XCHG_CTAS + cta, n);
   }
   if (threadIdx.x == 0) p.state[cta] = n;
   __syncthreads();

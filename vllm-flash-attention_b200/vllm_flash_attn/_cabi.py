@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("FA_B200_LIB", os.path.join(_HERE, "libfa_b200.so"))
 
 FA_OK = 0
 FA_ERR_WORKSPACE = -4
-ABI_VERSION = 4
+ABI_VERSION = 5
 FA_KERNEL_NONE, FA_KERNEL_TC5_PREFILL, FA_KERNEL_TILE, FA_KERNEL_DECODE = 0, 1, 2, 3
 OP_FWD, OP_VARLEN, OP_KVCACHE = 0, 1, 2
 
@@ -46,6 +46,7 @@ class FaFwdParams(C.Structure):
         ("rotary_dim", _i32), ("seqlen_ro", _i32), ("is_rotary_interleaved", _i32),
         ("num_splits", _i32), ("workspace", _vp), ("workspace_bytes", C.c_size_t), ("partial_out", _i32), ("kv_shard_start", _i32), ("kv_shard_len", _i32),
         ("num_sms", _i32), ("force_kernel", _i32), ("kernel_used", _i32), ("launches", _i32),
+        ("workspace_clean", _i32), ("fused_exchange", _vp),
     ]
 
 
@@ -54,7 +55,7 @@ EXPORTS = (
     "fa_b200_num_splits_heuristic", "fa_b200_workspace_bytes",
     "fa_b200_fwd", "fa_b200_varlen_fwd", "fa_b200_fwd_kvcache", "fa_b200_combine",
     "fa_b200_append_kv", "fa_b200_exchange_combine", "fa_b200_exchange_params_size",
-    "fa_b200_fwd_kvcache_static_scratch",
+    "fa_b200_fwd_kvcache_static_scratch", "fa_b200_fused_exchange_size",
 )
 STATIC_SCRATCH_BYTES = 4 << 20      # FA_B200_STATIC_SCRATCH_BYTES (include/fa_b200.h)
 
@@ -68,6 +69,12 @@ class FaExchangeParams(C.Structure):
                 ("rank", _i32), ("world", _i32), ("b", _i32), ("h", _i32), ("seqlen_q", _i32), ("d", _i32),
                 ("record_elems", _i64), ("o", _vp), ("softmax_lse", _vp),
                 ("o_batch_stride", _i64), ("o_row_stride", _i64), ("o_head_stride", _i64), ("out_dtype", _i32)]
+
+
+class FaFusedExchange(C.Structure):
+    """Mirror of FaFusedExchange (include/fa_b200.h): sequence-sharded decode in one kernel per rank."""
+    _fields_ = [("recv", _vp * FA_MAX_PEERS), ("flags", _vp * FA_MAX_PEERS), ("state", _vp), ("split_counters", _vp),
+                ("rank", _i32), ("world", _i32), ("max_units", _i32), ("unit_elems", _i64)]
 
 
 def _load():
@@ -95,6 +102,9 @@ def _load():
     lib.fa_b200_exchange_params_size.restype = C.c_size_t
     if lib.fa_b200_exchange_params_size() != C.sizeof(FaExchangeParams):
         raise ImportError("FaExchangeParams layout mismatch between libfa_b200.so and its binding")
+    lib.fa_b200_fused_exchange_size.restype = C.c_size_t
+    if lib.fa_b200_fused_exchange_size() != C.sizeof(FaFusedExchange):
+        raise ImportError("FaFusedExchange layout mismatch between libfa_b200.so and its binding")
     if lib.fa_b200_abi_version() != ABI_VERSION:
         raise ImportError("libfa_b200.so ABI version mismatch")
     if lib.fa_b200_params_size() != C.sizeof(FaFwdParams):

@@ -112,7 +112,14 @@ class PeerExchange:
     (b, h, seqlen_q, d) that will be merged; `merge()` then costs one kernel launch per decode step and
     is CUDA-graph replayable.  All ranks must call merge() the same number of times."""
 
-    def __init__(self, max_record_elems: int, device, group=None):
+    @classmethod
+    def for_decode(cls, max_batch: int, h: int, h_k: int, d: int, device, group=None, seqlen_q: int = 1):
+        """Exchange sized for decode steps of up to `max_batch` sequences with h / h_k heads of dimension d: both
+        the two-kernel record and the areas of the ONE-kernel path (fused_exchange)."""
+        return cls(partial_record_numel(max_batch, h, seqlen_q, d), device, group,
+                   fused_units=max_batch * h_k, fused_unit_elems=(seqlen_q * (h // h_k) * (d + 1) + 3) // 4 * 4)
+
+    def __init__(self, max_record_elems: int, device, group=None, *, fused_units: int = 0, fused_unit_elems: int = 0):
         import torch.distributed as dist
         single = not dist.is_initialized() or dist.get_world_size(group) == 1
         self.group = None if single else (group if group is not None else dist.group.WORLD)
@@ -125,7 +132,14 @@ class PeerExchange:
         self.off_flags = recv_elems                       # fp32/uint32 element offsets inside the allocation
         self.off_state = self.off_flags + 8 * _XCHG_CTAS  # flags [FA_MAX_PEERS][FA_XCHG_CTAS]
         self.off_local = self.off_state + _XCHG_CTAS      # state [FA_XCHG_CTAS]
-        total = self.off_local + self.record
+        # areas of the one-kernel path (include/fa_b200.h, FaFusedExchange); absent when fused_units == 0
+        self.fused_units, self.fused_unit_elems = int(fused_units), (int(fused_unit_elems) + 3) // 4 * 4
+        self.off_frecv = (self.off_local + self.record + 3) // 4 * 4
+        self.off_fflags = self.off_frecv + 2 * self.world * self.fused_units * self.fused_unit_elems
+        self.off_fstate = self.off_fflags + 8 * self.fused_units
+        self.off_fcount = self.off_fstate + self.fused_units
+        total = self.off_fcount + self.fused_units
+        self._fx = None
         if single:                                        # one rank: an ordinary allocation, same protocol
             self.buf = torch.zeros(total, dtype=torch.float32, device=device)
             self.handle = None
@@ -139,6 +153,23 @@ class PeerExchange:
             self.handle.barrier()                         # every rank's flags/state are zero before any push
             self.ptrs = [int(p) for p in self.handle.buffer_ptrs]
         self.local_record = self.buf[self.off_local:self.off_local + self.record]
+
+    def fused_params(self, b: int, h: int, h_k: int, sq: int, d: int):
+        """FaFusedExchange for a call of this shape, or None when the one-kernel areas are absent or too small."""
+        if self.fused_units == 0 or b * h_k > self.fused_units or sq * (h // h_k) * (d + 1) > self.fused_unit_elems:
+            return None
+        if self._fx is None:
+            from ._cabi import FaFusedExchange
+            fx = FaFusedExchange()
+            for r in range(self.world):
+                fx.recv[r] = self.ptrs[r] + 4 * self.off_frecv
+                fx.flags[r] = self.ptrs[r] + 4 * self.off_fflags
+            fx.state = self.ptrs[self.rank] + 4 * self.off_fstate
+            fx.split_counters = self.ptrs[self.rank] + 4 * self.off_fcount
+            fx.rank, fx.world = self.rank, self.world
+            fx.max_units, fx.unit_elems = self.fused_units, self.fused_unit_elems
+            self._fx = fx
+        return self._fx
 
     def merge(self, b: int, h: int, sq: int, d: int, out_dtype: torch.dtype, rec_elems: Optional[int] = None):
         """LSE-merge the records all ranks have staged in `local_record` (layout of
@@ -171,7 +202,7 @@ class PeerExchange:
 def flash_attn_with_kvcache_seq_sharded(q, k_cache, v_cache, cache_seqlens, block_table=None, *,
                                         shard_start: int, shard_end: int, group=None, softmax_scale=None,
                                         causal=False, alibi_slopes=None, num_splits=0, return_softmax_lse=False,
-                                        exchange: Optional["PeerExchange"] = None,
+                                        exchange: Optional["PeerExchange"] = None, one_kernel: Optional[bool] = None,
                                         _local_fn: Optional[Callable] = None, _merge_fn: Optional[Callable] = None):
     """Decode attention with the KV sequence sharded over the ranks of `group`.
 
@@ -180,8 +211,10 @@ def flash_attn_with_kvcache_seq_sharded(q, k_cache, v_cache, cache_seqlens, bloc
     seq_shard_range); `cache_seqlens` are the GLOBAL lengths.  Every rank returns the full result.
 
     With `exchange` (a PeerExchange created once for the group) the records travel by peer-memory
-    stores inside ONE fused push + wait + combine kernel instead of an NCCL all-gather followed by a
-    combine launch.
+    stores instead of an NCCL all-gather.  If the exchange was created with the one-kernel areas
+    (PeerExchange.for_decode) and they fit the call, the whole step is ONE kernel launch per rank: the decode
+    kernel merges its own splits, pushes the merged rows to the peers, waits for theirs and writes the final
+    result (`one_kernel=False` forces the older form: decode + split combine + a push / wait / combine kernel).
 
     seqlen_q must be 1 (or causal=False): with the last query token every key of the sequence is
     visible, so no cross-rank mask is needed.  ALiBi is rejected because its bias
@@ -196,6 +229,16 @@ def flash_attn_with_kvcache_seq_sharded(q, k_cache, v_cache, cache_seqlens, bloc
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     shard = (shard_start, shard_end)
     rec = partial_record_numel(b, h, sq, d)
+    if exchange is not None and _local_fn is None and one_kernel is not False:
+        fx = exchange.fused_params(b, h, k_cache.shape[2], sq, d)
+        if fx is not None:
+            from . import vllm_flash_attn_2_cuda as ext
+            scale = d ** -0.5 if softmax_scale is None else softmax_scale
+            out, lse = ext.fwd_kvcache(q, k_cache, v_cache, None, None, cache_seqlens, None, None, None, block_table, None, None,
+                                       scale, False, -1, -1, True, num_splits, _kv_shard=shard, _fused_exchange=fx)
+            return (out, lse) if return_softmax_lse else out
+        if one_kernel:
+            raise ValueError("one_kernel=True, but the PeerExchange has no one-kernel areas large enough for this call")
     if exchange is not None:
         if _local_fn is not None:
             _local_fn(exchange.local_record[:rec])

@@ -76,12 +76,13 @@ def _run(P: FaFwdParams, op: int, fn, device) -> None:
         need = lib.fa_b200_workspace_bytes(ref, op)
         if need == C.c_size_t(-1).value:
             check(-1)
-        ws = torch.empty(max(need, 16), dtype=torch.uint8, device=device)
-        P.workspace, P.workspace_bytes = ws.data_ptr(), ws.numel()
+        ws = torch.zeros(max(need, 16), dtype=torch.uint8, device=device)     # zeroed: workspace_clean (a memset node of the capture)
+        P.workspace, P.workspace_bytes, P.workspace_clean = ws.data_ptr(), ws.numel(), 1
         check(fn(ref, stream))
     else:
         key = (device.index, stream)
         ws = _ws_cache.get(key)
+        P.workspace_clean = 1       # the cached buffers are allocated zeroed and only the library writes to them
         if ws is not None:
             P.workspace, P.workspace_bytes = ws.data_ptr(), ws.numel()
         rc = fn(ref, stream)
@@ -89,7 +90,7 @@ def _run(P: FaFwdParams, op: int, fn, device) -> None:
             need = lib.fa_b200_workspace_bytes(ref, op)
             if need == C.c_size_t(-1).value:
                 check(-1)
-            ws = torch.empty(max(2 * need, 1 << 20), dtype=torch.uint8, device=device)
+            ws = torch.zeros(max(2 * need, 1 << 20), dtype=torch.uint8, device=device)
             _ws_cache[key] = ws
             P.workspace, P.workspace_bytes = ws.data_ptr(), ws.numel()
             rc = fn(ref, stream)
@@ -271,7 +272,8 @@ def varlen_fwd(q, k, v, out_, cu_seqlens_q, cu_seqlens_k, seqused_k, block_table
 
 def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_, cache_batch_idx_,
                 block_table_, alibi_slopes_, out_, softmax_scale, is_causal, window_size_left,
-                window_size_right, is_rotary_interleaved, num_splits, *, _partial_buf=None, _kv_shard=None) -> List[torch.Tensor]:
+                window_size_right, is_rotary_interleaved, num_splits, *, _partial_buf=None, _kv_shard=None,
+                _fused_exchange=None) -> List[torch.Tensor]:
     """mha_fwd_kvcache (flash_api.cpp:671-937).  q (b,sq,h,d); cache (b_c,sk,hk,d) or paged
     (num_blocks,page,hk,d) with block_table (b,max_blocks); optional new k/v (b,sk_new,hk,d) appended
     in place at cache_seqlens (with rotary on k and q).  Returns [out, softmax_lse].
@@ -279,7 +281,11 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
     ``_partial_buf`` (extension used by vllm_flash_attn.sharded): a 1-D fp32 tensor of
     b*h*sq*(d+1) elements; the call then runs in the C ABI's partial_out mode and writes the packed
     record [o (b,h,sq,d) | lse (b,h,sq)] into it (lse = -inf for rows with no key in this shard),
-    returning views of the two parts."""
+    returning views of the two parts.
+
+    ``_fused_exchange`` (extension used by vllm_flash_attn.sharded): a _cabi.FaFusedExchange; with ``_kv_shard`` set the
+    decode kernel then merges its splits, exchanges the merged rows with the peer GPUs and writes the FINAL out / lse
+    itself (one launch per decode step)."""
     _check_qkv(q, kcache, vcache)
     dev = q.device
     _chk(q.dim() == 4 and kcache.dim() == 4 and vcache.dim() == 4, "q, kcache, vcache must be 4-D")
@@ -346,6 +352,8 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
             P.o_batch_stride, P.o_row_stride, P.o_head_stride = out.stride(0), out.stride(1), out.stride(2)
         if _kv_shard is not None:           # (start, end): the cache holds that key range, seqlens_k are global
             P.kv_shard_start, P.kv_shard_len = int(_kv_shard[0]), int(_kv_shard[1] - _kv_shard[0])
+        if _fused_exchange is not None:
+            P.fused_exchange = C.addressof(_fused_exchange)
         P.b, P.seqlen_q, P.seqlen_k, P.h, P.h_k, P.d = b, sq, sk, h, hk, d
         P.is_bf16 = int(q.dtype == torch.bfloat16)
         P.softmax_scale = softmax_scale
