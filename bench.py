@@ -345,9 +345,15 @@ def run_ours(args):
     # ------------------------------------------------------------------ the two shardings (C4, C5), every N
     if args.sharded:
         torch.cuda.empty_cache()
-        line["c4"] = bench_c4(fa, ext, dev, world, rank, pk)
+        only = set(x for x in args.only.split(",") if x)
+        if not only or "c4" in only:
+            line["c4"] = bench_c4(fa, ext, dev, world, rank, pk)
         torch.cuda.empty_cache()
-        line["c5"] = {"b1": bench_c5(fa, ext, dev, world, rank, pk, batch=1), "b8": bench_c5(fa, ext, dev, world, rank, pk, batch=8)}
+        line["c5"] = {}
+        if not only or "c5b1" in only:
+            line["c5"]["b1"] = bench_c5(fa, ext, dev, world, rank, pk, batch=1)
+        if not only or "c5b8" in only:
+            line["c5"]["b8"] = bench_c5(fa, ext, dev, world, rank, pk, batch=8)
         torch.cuda.empty_cache()
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
@@ -642,6 +648,7 @@ def main():
     ap.add_argument("--no-decode", dest="decode", action="store_false")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-sharded", dest="sharded", action="store_false", help="skip the C4 / C5 sub-benchmarks")
+    ap.add_argument("--only", default="", help="development: comma list of c4,c5b1,c5b8 — run only those sub-benchmarks of the sharded section")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

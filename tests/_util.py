@@ -87,7 +87,9 @@ def ref_kernel_varlen(q, k, v, cu_q, cu_k, max_q, max_k, causal=False, window=(-
     P.is_causal, P.window_left, P.window_right = int(causal), window[0], window[1]
     P.cu_seqlens_q, P.cu_seqlens_k = cu_q.data_ptr(), cu_k.data_ptr()
     P.is_seqlens_k_cumulative = 1
-    need = lib.ref_fa2_workspace_bytes(C.byref(P))
+    # mha_varlen_fwd splits only in its GQA-swapped pure-decode form (flash_api.cpp:618-623); the glue's size query always
+    # reports the 128-split worst case, which for a long prefill batch is terabytes nobody will touch
+    need = lib.ref_fa2_workspace_bytes(C.byref(P)) if max_q == 1 else 16
     ws = torch.empty(need, dtype=torch.uint8, device=q.device)
     P.workspace, P.workspace_bytes = ws.data_ptr(), need
     rc = lib.ref_fa2_run(C.byref(P), 1, C.c_void_p(torch.cuda.current_stream().cuda_stream))

@@ -9,39 +9,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "tests")); sys.path.insert(0, os.path.join(ROOT, "tools"))
-from gpu_probe import C, run_case  # noqa: E402
-
-
-def random_spec(rng, i):
-    d = rng.choice([32, 64, 96, 128, 160, 192, 224, 256])
-    kind = rng.choice(["dense", "dense", "varlen", "varlen", "kvcache"])
-    hk = rng.choice([1, 2, 4]); h = hk * rng.choice([1, 2, 4])
-    causal = rng.random() < 0.5
-    window = (-1, -1)
-    local = not causal and rng.random() < 0.3
-    spec = C(f"fuzz{i}", 0, kind=kind, d=d, h=h, hk=hk, b=rng.randrange(1, 5), causal=causal, window=window,
-             dtype=rng.choice(["bf16", "fp16"]), alibi=rng.random() < 0.2, seed=i)
-    if kind == "kvcache":
-        spec["sq"] = rng.choice([1, 1, 2, 5, 40, 150, 300])
-        spec["sk"] = rng.randrange(spec["sq"] + 1, 1500)
-        spec["page"] = rng.choice([0, 16, 16, 32, 64, 128, 256])
-        spec["splits"] = rng.choice([0, 0, 0, 3]) if spec["sq"] * (h // hk) <= 16 else 0
-    else:
-        spec["sq"] = rng.randrange(1, 900)
-        spec["sk"] = spec["sq"] if rng.random() < 0.5 else rng.randrange(1, 1300)
-        if kind == "varlen":
-            spec["page"] = rng.choice([0, 0, 16, 32, 128, 256])
-            spec["mixed"] = rng.choice([0.0, 0.0, 0.5]) if spec["page"] or rng.random() < 0.5 else 0.0
-            spec["poison"] = bool(spec["page"])
-            if spec["mixed"] > 0:
-                spec["causal"], spec["window"] = True, (-1, -1)
-                spec["sk"] = max(spec["sk"], spec["sq"])
-    if local:   # the reference's tests draw window sizes below seqlen_k (tests/test_flash_attn.py:883): at or above it the
-        # host glue drops the window altogether (flash_api.cpp:289-294), which attention_ref does not model
-        # (varlen / kvcache draw per-sequence lengths down to sk/3, and the glue compares with the LONGEST sequence)
-        bound = max(spec["sk"] // 3, 1)
-        spec["window"] = (rng.randrange(0, bound), rng.randrange(0, bound))
-    return spec
+from parity_cases import random_spec, run_case  # noqa: E402
 
 
 def main():

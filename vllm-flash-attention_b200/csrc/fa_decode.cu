@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
       __threadfence();
       // c. merge the unit's splits into red / row_lse.  First the weights exp(lse_s - lse) of every (row, split) into
       // shared memory (one warp per row, lanes own splits); then every thread owns (row, 4-column) items and streams the
-      // splits with 8 independent 16-byte loads in flight — the partials sit in L2, and a walk with one or two loads in
+      // splits with 16 independent 16-byte loads in flight — the partials sit in L2, and a walk with one or two loads in
       // flight per lane is what made this tail cost more than the streaming loop of a short split.  Fixed order:
       // deterministic.
       const int S = p.num_splits;
@@ -321,6 +321,16 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
         const float* wr = wsm + r * S;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         int s2 = 0;
+        for (; s2 + 16 <= S; s2 += 16) {
+          float4 x[16];
+#pragma unroll
+          for (int u = 0; u < 16; u++) x[u] = __ldcg(reinterpret_cast<const float4*>(src + (s2 + u) * sstride * D));
+#pragma unroll
+          for (int u = 0; u < 16; u++) {
+            const float w = wr[s2 + u];
+            acc.x += w * x[u].x; acc.y += w * x[u].y; acc.z += w * x[u].z; acc.w += w * x[u].w;
+          }
+        }
         for (; s2 + 8 <= S; s2 += 8) {
           float4 x[8];
 #pragma unroll
@@ -372,7 +382,9 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
         const float l = row_lse[r];
         for (int w = 0; w < W; w++) p.xchg_recv[w][mine + Rw * D + r] = l;
       }
-      __threadfence_system();
+      // One system-scope release per flag: the CTA barrier orders every thread's row stores before the flag threads,
+      // and st.release.sys (fence + store) by a flag thread is cumulative over what it observed through the barrier —
+      // a separate __threadfence_system() by all threads before it would be a second fence round trip in series.
       __syncthreads();
       if (tid < W) {
         st_release_sys(p.xchg_flags[tid] + p.xchg_rank * p.xchg_max_units + unit, n);
