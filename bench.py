@@ -355,6 +355,10 @@ def run_ours(args):
         if not only or "c5b8" in only:
             line["c5"]["b8"] = bench_c5(fa, ext, dev, world, rank, pk, batch=8)
         torch.cuda.empty_cache()
+    if rank == 0 and world == 1 and args.ref_kernel:
+        torch.cuda.empty_cache()
+        line["ref_kernel"] = bench_ref_kernel(fa, dev)
+        torch.cuda.empty_cache()
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
         val, desc = cpu_attention_sample(threads, budget_s=30.0)
@@ -399,6 +403,61 @@ def bench_decode(fa, ext, dev, pk, pk_src, args, b=256, ctx=4096, page=16):
             "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
                          "traffic": ncu_traffic("decode_c3"), "peak_source": pk_src + " (copy)", "frac_of_nominal_8000": gbs / 8000.0,
                          "bytes_per_launch": nbytes}}
+
+
+def bench_ref_kernel(fa, dev, iters=20):
+    """BASELINE.md section 3's "reference kernel on B200" column, driver-run: the REFERENCE's own FA2 forward kernels,
+    compiled for sm_100 from /root/reference by oracle/Makefile into oracle/_ref (test infrastructure: loaded only
+    inside this leg, outside the product's timed regions — like cpu_baseline), next to ours on the same box and the
+    same tensors: C1 (latency), C2 (TFLOP/s), C3 (GB/s).  None when the library was not built."""
+    import torch
+    import _util
+    if _util.ref_lib() is None:
+        return None
+
+    def t(f, n=iters):
+        for _ in range(5):
+            f()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            f()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+
+    dt = torch.bfloat16
+    g = torch.Generator(device=dev).manual_seed(0)
+    res = {"what": "reference FA2 kernels (csrc/flash_attn/src, mma.sync) recompiled for sm_100 from /root/reference, same box, same tensors; "
+                   "CUDA events over back-to-back calls through each library's Python entry"}
+    q = torch.randn(2, 512, 8, 64, device=dev, dtype=dt, generator=g); k = torch.randn_like(q); v = torch.randn_like(q)
+    ms_o, ms_r = t(lambda: fa.flash_attn_func(q, k, v), 200), t(lambda: _util.ref_kernel_fwd(q, k, v), 200)
+    res["c1"] = {"workload": "C1 dense B=2 S=512 H=8 D=64 non-causal", "ours_us_per_call": ms_o * 1e3, "ref_kernel_us_per_call": ms_r * 1e3,
+                 "speedup": ms_r / ms_o}
+    tot = sum(SEQLENS_C2)
+    q = torch.randn(tot, H, D, device=dev, dtype=dt, generator=g)
+    k = torch.randn(tot, HK, D, device=dev, dtype=dt, generator=g); v = torch.randn(tot, HK, D, device=dev, dtype=dt, generator=g)
+    cu = torch.tensor([0] + list(__import__("itertools").accumulate(SEQLENS_C2)), dtype=torch.int32, device=dev)
+    mx = max(SEQLENS_C2)
+    ms_o = t(lambda: fa.flash_attn_varlen_func(q, k, v, cu, cu, mx, mx, causal=True))
+    ms_r = t(lambda: _util.ref_kernel_varlen(q, k, v, cu, cu, mx, mx, causal=True))
+    fl = prefill_flops()
+    res["c2"] = {"workload": "C2 varlen causal 32q/8kv D=128, 16384 tokens", "ours_tflops": fl / (ms_o * 1e-3) / 1e12,
+                 "ref_kernel_tflops": fl / (ms_r * 1e-3) / 1e12, "ours_ms": ms_o, "ref_kernel_ms": ms_r, "speedup": ms_r / ms_o}
+    del q, k, v
+    b, ctx, page = 256, 4096, 16
+    nblk = b * (ctx // page) * 5 // 4
+    kc = torch.randn(nblk, page, HK, D, device=dev, dtype=dt, generator=g); vc = torch.randn(nblk, page, HK, D, device=dev, dtype=dt, generator=g)
+    bt = torch.randperm(nblk, device=dev, generator=g)[: b * (ctx // page)].to(torch.int32).view(b, -1).contiguous()
+    q = torch.randn(b, 1, H, D, device=dev, dtype=dt, generator=g)
+    lens = torch.full((b,), ctx, dtype=torch.int32, device=dev)
+    ms_o = t(lambda: fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=lens, block_table=bt, causal=True))
+    ms_r = t(lambda: _util.ref_kernel_kvcache(q, kc, vc, lens, bt, causal=True))
+    nb = 2.0 * b * ctx * HK * D * 2
+    res["c3"] = {"workload": "C3 paged decode B=256 ctx 4096 block 16", "ours_gbs": nb / (ms_o * 1e-3) / 1e9,
+                 "ref_kernel_gbs": nb / (ms_r * 1e-3) / 1e9, "ours_ms": ms_o, "ref_kernel_ms": ms_r, "speedup": ms_r / ms_o}
+    return res
 
 
 # ------------------------------------------------------------------------------------------------
@@ -647,6 +706,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-decode", dest="decode", action="store_false")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-ref-kernel", dest="ref_kernel", action="store_false", help="skip the reference-kernel comparison leg (N=1)")
     ap.add_argument("--no-sharded", dest="sharded", action="store_false", help="skip the C4 / C5 sub-benchmarks")
     ap.add_argument("--only", default="", help="development: comma list of c4,c5b1,c5b8 — run only those sub-benchmarks of the sharded section")
     args = ap.parse_args()

@@ -10,7 +10,6 @@
 #include <climits>
 #include <cstring>
 #include <map>
-#include <mutex>
 #include <utility>
 #include <vector>
 #include "fa_b200.h"
@@ -79,17 +78,17 @@ static bool as_single_page(const FaFwdParams* a, int op, KParams* k) {
   return true;
 }
 
-// Side stream + fork / join events for the decode half of a mixed varlen batch, one set per (device, caller
-// stream).  Created on first use and kept for the life of the process (a handful of streams in practice).
+// Side stream + fork / join events for the decode half of a mixed varlen batch, one set per (host thread, device,
+// caller stream).  Created on first use and kept for the life of the process (a handful of streams in practice).
 // The fork / join pattern is capture-safe: under stream capture the side stream joins the capture at the fork
 // event and leaves it at the join event.
 struct ForkSet { cudaStream_t side; cudaEvent_t fork, join; };
 static ForkSet* get_fork_set(cudaStream_t main) {
-  static std::mutex mu;
-  static std::map<std::pair<int, cudaStream_t>, ForkSet> sets;
+  // per host thread: two threads that issue on the same stream must not share the fork / join events (an event records
+  // the LAST cudaEventRecord: thread B's record between thread A's record and wait would let A's side stream start early)
+  static thread_local std::map<std::pair<int, cudaStream_t>, ForkSet> sets;
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
-  std::lock_guard<std::mutex> lock(mu);
   auto key = std::make_pair(dev, main);
   auto it = sets.find(key);
   if (it != sets.end()) return &it->second;

@@ -27,6 +27,7 @@
 #include "fa_common.cuh"
 #include "fa_sm100.cuh"
 #include <algorithm>
+#include <cstring>
 #include <type_traits>
 #include <vector>
 #include "fa_launch.h"
@@ -607,6 +608,18 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, int box_rows, 
                      int64_t head_stride, int64_t row_stride, int64_t batch_stride) {
   EncodeTiledFn fn = get_encode_fn();
   if (!fn) return false;
+  // Encoding a map costs ~1-2 us of host time and a prefill launch needs four; a serving loop calls with the same
+  // tensors (KV pool, preallocated q / out) over and over, so the last few encodings are kept per host thread, keyed
+  // on everything that enters the descriptor.  A CUtensorMap is a plain 128-byte value: a cached copy is as good as
+  // a fresh one as long as the key matches.
+  struct Key { const void* base; int bf16, box_rows, d, heads, batch; int64_t rows, hs, rs, bs; };
+  struct Slot { Key k; CUtensorMap m; bool used; };
+  constexpr int NSLOT = 16;
+  static thread_local Slot cache[NSLOT] = {};
+  static thread_local unsigned next = 0;
+  const Key key{base, bf16 ? 1 : 0, box_rows, d, heads, batch, rows, head_stride, row_stride, batch_stride};
+  for (int i = 0; i < NSLOT; i++)
+    if (cache[i].used && memcmp(&cache[i].k, &key, sizeof(Key)) == 0) { *m = cache[i].m; return true; }
   cuuint64_t dims[4] = {(cuuint64_t)d, (cuuint64_t)heads, (cuuint64_t)rows, (cuuint64_t)batch};
   cuuint64_t strides[3] = {(cuuint64_t)head_stride * 2, (cuuint64_t)row_stride * 2,
                            (cuuint64_t)(batch > 1 ? batch_stride : row_stride * rows) * 2};
@@ -615,7 +628,11 @@ static bool make_map(CUtensorMap* m, const void* base, bool bf16, int box_rows, 
   CUresult r = fn(m, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
                   const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS;
+  if (r != CUDA_SUCCESS) return false;
+  Slot& s = cache[next++ % NSLOT];
+  memset(&s.k, 0, sizeof(Key));          // padding bytes take part in the memcmp
+  s.k = key; s.m = *m; s.used = true;
+  return true;
 }
 
 bool tc5_supported(const KParams& p) {

@@ -11,6 +11,7 @@ Kernels are enqueued on torch's current CUDA stream of q's device, no host synch
 from __future__ import annotations
 
 import ctypes as C
+import threading
 from typing import List, Optional
 
 import torch
@@ -19,7 +20,48 @@ from . import _cabi
 from ._cabi import FaFwdParams, OP_FWD, OP_KVCACHE, OP_VARLEN, check, lib
 
 _force_kernel = 0          # tests: _cabi.FA_KERNEL_* to pin a kernel family
-last_call_info = {}        # diagnostics of the most recent call (kernel_used, num_splits, launches)
+
+
+class _PerThreadInfo:
+    """Mapping with one dict per host thread: the diagnostics of the most recent call ON THIS THREAD (kernel_used,
+    num_splits, launches).  The reference's extension keeps no global mutable state (flash_api.cpp: plain functions),
+    so neither does this module: two threads driving two streams never see each other's values."""
+
+    def __init__(self):
+        self._tls = threading.local()
+
+    def _d(self):
+        d = getattr(self._tls, "d", None)
+        if d is None:
+            d = self._tls.d = {}
+        return d
+
+    def __getitem__(self, k):
+        return self._d()[k]
+
+    def get(self, k, default=None):
+        return self._d().get(k, default)
+
+    def update(self, *a, **kw):
+        self._d().update(*a, **kw)
+
+    def keys(self):
+        return self._d().keys()
+
+    def items(self):
+        return self._d().items()
+
+    def __iter__(self):
+        return iter(self._d())
+
+    def __len__(self):
+        return len(self._d())
+
+    def __repr__(self):
+        return repr(self._d())
+
+
+last_call_info = _PerThreadInfo()
 
 
 def _chk(cond: bool, msg: str) -> None:
@@ -61,12 +103,13 @@ def _alibi(P, alibi_slopes, batch, heads, device):
     P.alibi_slopes_batch_stride = alibi_slopes.stride(0) if alibi_slopes.dim() == 2 else 0
 
 
-_ws_cache = {}             # (device index, stream handle) -> persistent workspace tensor
+_ws_cache = {}             # (device index, stream handle, host thread) -> persistent workspace tensor (zero-initialised)
 
 
 def _run(P: FaFwdParams, op: int, fn, device) -> None:
-    """One library call.  The split-KV / work-list workspace is a persistent per-(device, stream)
-    buffer (calls on one stream are ordered, so they can share it), grown when the library says it is
+    """One library call.  The split-KV / work-list workspace is a persistent per-(device, stream, host thread)
+    buffer (calls one thread makes on one stream are ordered, so they can share it; two threads issuing on the
+    same stream get a buffer each and never race on the prefill work list), grown when the library says it is
     too small; under CUDA-graph capture a private buffer sized by fa_b200_workspace_bytes is used
     instead, so that the capture owns it."""
     P.force_kernel = _force_kernel
@@ -80,7 +123,7 @@ def _run(P: FaFwdParams, op: int, fn, device) -> None:
         P.workspace, P.workspace_bytes, P.workspace_clean = ws.data_ptr(), ws.numel(), 1
         check(fn(ref, stream))
     else:
-        key = (device.index, stream)
+        key = (device.index, stream, threading.get_ident())
         ws = _ws_cache.get(key)
         P.workspace_clean = 1       # the cached buffers are allocated zeroed and only the library writes to them
         if ws is not None:
