@@ -121,7 +121,7 @@ typedef struct FaFwdParams {
   int32_t rotary_dim, seqlen_ro, is_rotary_interleaved;
 
   /* ---- split-KV ---- */
-  int32_t num_splits;    /* in: 0 = heuristic, >=1 forced; out: splits used */
+  int32_t num_splits;    /* in: 0 = heuristic, >=1 forced; out: splits used (mixed varlen batch: by its decode half) */
   void* workspace;       /* >= fa_b200_workspace_bytes(p) bytes, or NULL when that is 0 */
   size_t workspace_bytes;
   /* fwd_kvcache only.  1 = partial-result mode for a KV range that is one shard of a longer

@@ -332,6 +332,42 @@ def test_varlen_empty_sequences_through_the_work_list():
     assert info["kernel_used"] == 1
 
 
+def test_mixed_batch_with_few_kv_heads_splits_its_decode_half():
+    """A tensor-parallel shard of a mixed batch (C4 at TP = 8: 8 q heads / 1 kv head): one decode CTA per (sequence,
+    kv head) would leave most SMs idle, so the decode half is split along the context and merged inside the decode
+    kernel — same launches as before, partials behind the work list in the same workspace.  Paged cache with NaN in
+    every row past a sequence's length; empty and one-key contexts next to 4096-key ones."""
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import vllm_flash_attn_2_cuda as ext
+    torch.manual_seed(11)
+    dev, dt, h, hk, d, page = "cuda", torch.bfloat16, 8, 1, 128, 16
+    lens_q = [300, 1, 1, 2, 1, 700, 1, 1, 1, 2]
+    lens_k = [300, 3000, 4096, 1500, 17, 700, 1, 0, 2500, 4095]
+    nb = len(lens_q); mb = (max(lens_k) + page - 1) // page
+    cu_q = torch.tensor([0] + list(torch.tensor(lens_q).cumsum(0)), dtype=torch.int32)
+    cu_k = torch.tensor([0] + list(torch.tensor(lens_k).cumsum(0)), dtype=torch.int32)
+    q = torch.randn(sum(lens_q), h, d, device=dev, dtype=dt)
+    k = torch.randn(sum(lens_k), hk, d, device=dev, dtype=dt); v = torch.randn_like(k)
+    bt = torch.randperm(nb * mb, device=dev).to(torch.int32).view(nb, mb).contiguous()
+    kc = torch.full((nb * mb, page, hk, d), float("nan"), device=dev, dtype=dt); vc = torch.full_like(kc, float("nan"))
+    for i in range(nb):
+        for j in range(lens_k[i]):
+            blk = int(bt[i, j // page])
+            kc[blk, j % page] = k[int(cu_k[i]) + j]; vc[blk, j % page] = v[int(cu_k[i]) + j]
+    out = fa.flash_attn_varlen_func(q, kc, vc, cu_q.to(dev), cu_k.to(dev), max(lens_q), max(lens_k), causal=True, block_table=bt)
+    info = dict(ext.last_call_info)
+    assert info["kernel_used"] == 1 and info["launches"] == 3 and info["num_splits"] > 1, info
+    ref32, _ = orc.attention_ref_varlen(q, k, v, cu_q, cu_k, causal=True)
+    pt, _ = orc.attention_ref_varlen(q, k, v, cu_q, cu_k, causal=True, upcast=False, reorder_ops=True)
+    err = (out.float() - ref32.float()).abs().max().item(); err_pt = (pt.float() - ref32.float()).abs().max().item()
+    assert not torch.isnan(out.float()).any()
+    assert err <= 2 * err_pt + 1e-5, (err, err_pt, info)
+    # twice more through the same cached workspace: the arrival counters must be back at zero, results identical
+    for _ in range(2):
+        again = fa.flash_attn_varlen_func(q, kc, vc, cu_q.to(dev), cu_k.to(dev), max(lens_q), max(lens_k), causal=True, block_table=bt)
+        assert torch.equal(again, out)
+
+
 def test_varlen_many_sequences_mixed():
     """1500 sequences (more than the schedule kernel's thread count), mostly short: single-token and
     few-token sequences go to the decode kernel, the rest to the tcgen05 kernel, a handful of long ones

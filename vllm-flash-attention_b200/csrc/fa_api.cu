@@ -110,6 +110,9 @@ struct Plan {
   bool fused_tail;   // decode kernel merges its own splits (and exchanges across GPUs): no separate combine launch
   size_t lse_floats, o_floats;   // split workspace payload: lse block (padded to 4 floats) | o block | [arrival counters]
   bool counters_in_head;
+  int mixed_splits;            // mixed varlen batch: split count of the decode half (>= 1)
+  size_t mixed_part_off;       // ... byte offset of its partials in the workspace (behind the prefill work list)
+  size_t mixed_lse_floats;
 };
 static_assert(FA_MAX_PEERS == FA_KP_MAX_PEERS, "peer capacity of the C ABI and of KParams must agree");
 
@@ -159,6 +162,7 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   k.cache_batch_idx = a->cache_batch_idx;
   k.seqlen_knew = a->seqlen_knew;   // rows already appended by fa_b200_append_kv
   k.lse_seq_stride = a->seqlen_q;
+  k.part_seq_stride = a->seqlen_q;
   k.min_rows = 0; k.max_rows = INT_MAX;
   FA_CHECK(a->kv_shard_len >= 0 && a->kv_shard_start >= 0 && (a->kv_shard_len == 0 || op == OP_KVCACHE), "kv_shard_* is only valid for fwd_kvcache");
   k.kv_shard_start = a->kv_shard_start; k.kv_shard_len = a->kv_shard_len;
@@ -261,10 +265,26 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   pl->counters_in_head = (size_t)a->b * a->h_k * sizeof(int) <= FA_B200_WS_HEAD_BYTES;
   pl->ws_bytes = splits > 1 ? FA_B200_WS_HEAD_BYTES + (pl->lse_floats + pl->o_floats) * sizeof(float) +
                               ((pl->fused_tail && !fx && !pl->counters_in_head) ? (size_t)a->b * a->h_k * sizeof(int) : 0) : 0;
+  pl->mixed_splits = 1; pl->mixed_part_off = 0; pl->mixed_lse_floats = 0;
   if (kernel == FA_KERNEL_TC5_PREFILL) {
     if (op == OP_VARLEN) FA_CHECK(a->total_q > 0, "total_q (rows of q) must be given for varlen_fwd");
     pl->ws_bytes = tc5_workspace_bytes(k, a->total_q, num_sms);    // cost-sorted work list of the persistent kernel
     if (pl->ws_bytes) pl->ws_bytes += FA_B200_WS_HEAD_BYTES;
+    // Decode half of a mixed batch: with few (sequence, kv head) units — a TP shard holding one or two KV heads — one CTA
+    // per unit leaves SMs idle and the longest context sets the time, so the half is split like a kvcache decode
+    // (the reference consults the same heuristic for its GQA-packed varlen decode, flash_api.cpp:618-623).  Which
+    // sequences are short is only known on the device: the count is taken as if all were.
+    if (pl->decode_rows > 0 && a->seqlen_k > 0 && (size_t)a->b * a->h_k * sizeof(int) <= FA_B200_WS_HEAD_BYTES) {
+      const int ms = fa_b200_num_splits_heuristic(a->b * a->h_k, num_sms * 2, (a->seqlen_k + 255) / 256, 8);
+      if (ms > 1) {
+        const int pos = std::max(1, pl->decode_rows / k.group);                 // query positions a decode-half sequence can have
+        const size_t prow = (size_t)ms * a->b * a->h * pos;
+        pl->mixed_splits = ms;
+        pl->mixed_lse_floats = (prow + 3) / 4 * 4;
+        pl->mixed_part_off = ((pl->ws_bytes ? pl->ws_bytes : (size_t)FA_B200_WS_HEAD_BYTES) + 15) / 16 * 16;
+        pl->ws_bytes = pl->mixed_part_off + (pl->mixed_lse_floats + prow * a->d) * sizeof(float);
+      }
+    }
   }
   return FA_OK;
 }
@@ -275,7 +295,7 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
   Plan pl;
   int rc = make_plan(a, op, &pl);
   if (rc != FA_OK) return rc;
-  a->kernel_used = pl.kernel; a->num_splits = pl.num_splits; a->launches = 0;
+  a->kernel_used = pl.kernel; a->num_splits = pl.mixed_splits > 1 ? pl.mixed_splits : pl.num_splits; a->launches = 0;
   KParams& k = pl.k;
   if (a->seqlen_q == 0 || a->b == 0) return FA_OK;
   if (pl.num_splits > 1) {
@@ -307,14 +327,17 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
     case FA_KERNEL_DECODE: e = launch_decode(k, pl.is_bf16, stream); break;
     case FA_KERNEL_TILE: e = launch_tile(k, pl.is_bf16, stream); break;
     case FA_KERNEL_TC5_PREFILL: {
+      const bool have_list = tc5_workspace_bytes(k, a->total_q, pl.num_sms) != 0;
       if (pl.ws_bytes) {
         if (a->workspace == nullptr || a->workspace_bytes < pl.ws_bytes)
           return fail(FA_ERR_WORKSPACE, "work-list workspace too small: need %zu bytes, got %zu", pl.ws_bytes, a->workspace_bytes);
-        if ((reinterpret_cast<uintptr_t>(a->workspace) & 7) != 0) return fail(FA_ERR_INVALID, "workspace must be 8-byte aligned");
+        if ((reinterpret_cast<uintptr_t>(a->workspace) & 15) != 0) return fail(FA_ERR_INVALID, "workspace must be 16-byte aligned");
+      }
+      if (have_list) {
         k.work_header = reinterpret_cast<int*>(reinterpret_cast<char*>(a->workspace) + FA_B200_WS_HEAD_BYTES);
         k.work_items = reinterpret_cast<int2*>(reinterpret_cast<char*>(a->workspace) + FA_B200_WS_HEAD_BYTES + 16);
       }
-      a->launches = pl.ws_bytes ? 1 : 0;
+      a->launches = have_list ? 1 : 0;
       // ---- decode half of a mixed batch: forked onto a side stream, ahead of the prefill launches.  A batch
       // without short sequences (a plain prefill) then pays nothing on its own stream for the decode launches that
       // find no work, and in a mixed batch the tails of the two halves overlap instead of running back to back.
@@ -334,6 +357,16 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
         if (fs && cudaEventRecord(fs->fork, stream) == cudaSuccess && cudaStreamWaitEvent(fs->side, fs->fork, 0) == cudaSuccess) ds = fs->side;
         else fs = nullptr;                              // no side stream: same launches, in order, on the caller's stream
         KParams kd = k;
+        if (pl.mixed_splits > 1) {
+          // split decode half: partials behind the work list, arrival counters in the workspace head, merged in-kernel
+          kd.num_splits = pl.mixed_splits;
+          kd.part_seq_stride = std::max(1, cap / g);
+          kd.lse_accum = reinterpret_cast<float*>(reinterpret_cast<char*>(a->workspace) + pl.mixed_part_off);
+          kd.o_accum = kd.lse_accum + pl.mixed_lse_floats;
+          kd.split_counters = reinterpret_cast<int*>(a->workspace);
+          if (!a->workspace_clean && cudaMemsetAsync(kd.split_counters, 0, (size_t)a->b * a->h_k * sizeof(int), ds) != cudaSuccess)
+            return fail(FA_ERR_CUDA, "mixed batch: clearing the split arrival counters failed");
+        }
         if (g <= lo_rows) {
           kd.min_rows = 0; kd.max_rows = lo_rows;
           e = launch_decode(kd, pl.is_bf16, ds);

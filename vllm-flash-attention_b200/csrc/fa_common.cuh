@@ -34,6 +34,8 @@ struct KParams {
   int seqlen_knew;                              // keys appended this call (already in cache)
   int num_splits;
   int lse_seq_stride;                           // seqlen_q used for lse/accum row indexing
+  int part_seq_stride;                          // query positions per (split, b, h) in the decode kernel's split partials (= lse_seq_stride,
+                                                // except for the decode half of a mixed batch, whose sequences have only a few positions)
   int min_rows, max_rows;                        // serve only sequences with min_rows <= seqlen_q*group <= max_rows (mixed batches)
   int kv_shard_start, kv_shard_len;               // sequence-sharded decode: this rank holds keys [start, start+len) of every sequence (len 0 = off)
   int2* work_items; int* work_header;           // tcgen05 prefill: cost-sorted (sequence, m_block) list + {draw counter, count}; NULL = static order

@@ -257,7 +257,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
       for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
         const int r = idx / (D / 4), c4 = idx % (D / 4);
         int qpos; const int hd = head_of(r, qpos);
-        const int64_t orow = (((int64_t)split * p.b + bidb) * p.h + hd) * p.lse_seq_stride + qpos;
+        const int64_t orow = (((int64_t)split * p.b + bidb) * p.h + hd) * p.part_seq_stride + qpos;
         const float inv = row_inv[r];
         float4 x = *reinterpret_cast<const float4*>(red + r * Cfg::RED_STRIDE + c4 * 4);
         x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
       }
       for (int r = tid; r < Rw; r += NW * 32) {
         int qpos; const int hd = head_of(r, qpos);
-        p.lse_accum[(((int64_t)split * p.b + bidb) * p.h + hd) * p.lse_seq_stride + qpos] = row_lse[r];
+        p.lse_accum[(((int64_t)split * p.b + bidb) * p.h + hd) * p.part_seq_stride + qpos] = row_lse[r];
       }
       // b. arrival ticket: the last CTA of the unit carries on, the others are done
       __threadfence();
@@ -284,11 +284,11 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
       // flight per lane is what made this tail cost more than the streaming loop of a short split.  Fixed order:
       // deterministic.
       const int S = p.num_splits;
-      const int64_t sstride = (int64_t)p.b * p.h * p.lse_seq_stride;
+      const int64_t sstride = (int64_t)p.b * p.h * p.part_seq_stride;
       float* wsm = red + ROWS * Cfg::RED_STRIDE;            // [Rw][S] weights, behind the O rows (the ring is free by now)
       for (int r = warp; r < Rw; r += NW) {
         int qpos; const int hd = head_of(r, qpos);
-        const int64_t row0 = ((int64_t)bidb * p.h + hd) * p.lse_seq_stride + qpos;
+        const int64_t row0 = ((int64_t)bidb * p.h + hd) * p.part_seq_stride + qpos;
         float ls[4], mx = -INFINITY;
 #pragma unroll
         for (int i = 0; i < 4; i++) {
@@ -317,7 +317,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
       for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
         const int r = idx / (D / 4), c4 = idx % (D / 4);
         int qpos; const int hd = head_of(r, qpos);
-        const float* src = p.o_accum + (((int64_t)bidb * p.h + hd) * p.lse_seq_stride + qpos) * D + c4 * 4;
+        const float* src = p.o_accum + (((int64_t)bidb * p.h + hd) * p.part_seq_stride + qpos) * D + c4 * 4;
         const float* wr = wsm + r * S;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         int s2 = 0;

@@ -212,13 +212,20 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
       }
       published++;
     };
-    // The mailbox runs one unit ahead of the loads: unit u+1 is drawn and published before the loads of
-    // unit u are issued, so the other roles never wait for the scheduler at a unit boundary.
+    // Unit u+1 is drawn once the loads of unit u are all issued — the ring lets the producer run two KV iterations
+    // ahead of the MMAs, which covers the draw (one atomic and three dependent loads), so the other roles still find the
+    // next unit in the mailbox at a unit boundary.  Drawing it BEFORE unit u's loads (as this loop first did) commits a
+    // CTA to its next unit a whole unit early: with only a few units per CTA (a TP shard: 256 units on 148 CTAs) every
+    // CTA then holds two units from the first microsecond on, the cost-sorted list degenerates into a static
+    // assignment (measured: 24 KV iterations on the longest CTA, 10 on the shortest, where list scheduling gives 16),
+    // and a launch pays two draws in series before its first Q load.
     Tc5Work wk = fetch();
     publish(wk);
     for (int unit_idx = 0; wk.valid; unit_idx++) {
+#ifdef FA_TC5_EARLY_DRAW
       const Tc5Work nxt = fetch();
       publish(nxt);
+#endif
 
       const int m0 = wk.m_block * Cfg::UNIT_ROWS, sq = wk.sq, sk = wk.sk;
       const int kvh = wk.head / p.group;
@@ -348,6 +355,10 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
           }
         }
       }
+#ifndef FA_TC5_EARLY_DRAW
+      const Tc5Work nxt = fetch();
+      publish(nxt);
+#endif
       wk = nxt;
     }
     __syncwarp();
@@ -389,6 +400,10 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
         long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
         p.trace[(2 * 128 + 127) * 16 + 12] = clock64(); p.trace[(2 * 128 + 127) * 16 + 13] = ns;
       }
+      if (p.trace) {                // every CTA: wall-clock start / end, KV iterations, units (behind the CTA-0 timeline)
+        long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+        p.trace[3 * 128 * 16 + blockIdx.x * 4 + 0] = ns;
+      }
 #endif
       for (int wi = 0;; wi++) {
         const int ms = wi & 1;
@@ -401,6 +416,12 @@ fa_prefill_tc5_kernel(const __grid_constant__ KParams p, const __grid_constant__
           long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
           p.trace[(2 * 128 + 127) * 16 + 14] = clock64(); p.trace[(2 * 128 + 127) * 16 + 15] = ns;
           p.trace[(2 * 128 + 127) * 16 + 11] = trace_it;
+        }
+        if (!wk.valid && p.trace) {
+          long long ns; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns));
+          p.trace[3 * 128 * 16 + blockIdx.x * 4 + 1] = ns;
+          p.trace[3 * 128 * 16 + blockIdx.x * 4 + 2] = trace_it;
+          p.trace[3 * 128 * 16 + blockIdx.x * 4 + 3] = wi;
         }
 #endif
         if (!wk.valid) break;
@@ -693,7 +714,7 @@ size_t tc5_workspace_bytes(const KParams& p, int64_t total_q, int num_sms) {
 static cudaError_t launch_prefill_tc5_impl(const KParams& p, bool is_bf16, int64_t total_q, int64_t total_k, int num_sms, cudaStream_t stream);
 cudaError_t launch_prefill_tc5(const KParams& p_in, bool is_bf16, int64_t total_q, int64_t total_k, int num_sms, cudaStream_t stream) {
   static long long* buf = nullptr;
-  const size_t n = 3 * 128 * 16;
+  const size_t n = 3 * 128 * 16 + 4 * 160;
   if (!buf) cudaMalloc(&buf, n * sizeof(long long));
   cudaMemsetAsync(buf, 0, n * sizeof(long long), stream);
   KParams p = p_in; p.trace = buf;
