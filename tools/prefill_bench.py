@@ -71,6 +71,12 @@ def main():
     print(json.dumps({"config": "C2 varlen mixed 16k", "ms": ms, "TFLOPs": flops / (ms * 1e-3)}), flush=True)
     if a.quick:
         return
+    for hq, hk, b, s in ((32, 8, 8, 2048), (64, 8, 4, 2048), (32, 8, 2, 8192)):   # GQA: head-pair work units
+        for causal in (True, False):
+            q = torch.randn(b, s, hq, 128, device=dev, dtype=dt); k = torch.randn(b, s, hk, 128, device=dev, dtype=dt); v = torch.randn_like(k)
+            fl = 4.0 * b * s * s * hq * 128 / (2 if causal else 1) / 1e12
+            ms = timeit(lambda: fa.flash_attn_func(q, k, v, causal=causal), a.iters)
+            print(json.dumps({"config": f"gqa d128 {hq}q/{hk}kv b{b} s{s} causal={causal}", "ms": ms, "TFLOPs": fl / (ms * 1e-3)}), flush=True)
     for d, h in ((128, 16), (64, 32)):
         for causal in (False, True):
             for s in (2048, 8192):
