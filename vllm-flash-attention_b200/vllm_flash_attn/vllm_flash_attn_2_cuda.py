@@ -7,10 +7,17 @@ What lives here is only what needs torch: device/dtype/shape checks on tensors, 
 normalisation, kernel choice, split heuristic, launches) is in the library (csrc/fa_api.cu).
 Kernels are enqueued on torch's current CUDA stream of q's device, no host synchronisation
 (flash_api.cpp:344,399).
+
+Two host bindings over the same library: when the compiled pybind11 / ATen module ``_fa_torch`` (csrc/fa_torch_ext.cpp,
+built by build_torch_ext.sh — the form the reference's own extension has) is present, the three plain ops go through it
+(a few microseconds of host time per call instead of ~25 through ctypes); the Python-over-ctypes implementation below
+is the same logic, serves when that module was not built, and carries the sharding / test extensions
+(``_partial_buf``, ``_kv_shard``, ``_fused_exchange``, ``_force_kernel``).  ``FA_B200_HOST=ctypes`` forces it.
 """
 from __future__ import annotations
 
 import ctypes as C
+import os
 import threading
 from typing import List, Optional
 
@@ -20,6 +27,18 @@ from . import _cabi
 from ._cabi import FaFwdParams, OP_FWD, OP_KVCACHE, OP_VARLEN, check, lib
 
 _force_kernel = 0          # tests: _cabi.FA_KERNEL_* to pin a kernel family
+
+try:
+    from . import _fa_torch as _N        # compiled host binding (optional; same library underneath)
+    if _N.abi_version() != _cabi.ABI_VERSION:
+        raise ImportError(f"_fa_torch was built against ABI {_N.abi_version()}, libfa_b200.so has {_cabi.ABI_VERSION}: "
+                          "rebuild with build_torch_ext.sh")
+except ModuleNotFoundError:
+    _N = None
+_NATIVE = _N               # the loaded module, whatever _N is switched to later (tests toggle _N)
+if os.environ.get("FA_B200_HOST", "") == "ctypes":
+    _N = None
+host_binding = "pybind11" if _N is not None else "ctypes"
 
 
 class _PerThreadInfo:
@@ -34,7 +53,14 @@ class _PerThreadInfo:
         d = getattr(self._tls, "d", None)
         if d is None:
             d = self._tls.d = {}
+        if getattr(self._tls, "native", False):      # the last call on this thread went through _fa_torch
+            self._tls.native = False
+            ku, ns, ln = _NATIVE.last_call_info()
+            d.update(kernel_used=ku, num_splits=ns, launches=ln)
         return d
+
+    def _native_call(self):
+        self._tls.native = True
 
     def __getitem__(self, k):
         return self._d()[k]
@@ -178,6 +204,18 @@ def _pad_head(x, d_pad):
 
 def fwd(q, k, v, out_, alibi_slopes_, p_dropout, softmax_scale, is_causal, window_size_left,
         window_size_right, return_softmax, gen_) -> List[torch.Tensor]:
+    """mha_fwd (flash_api.cpp:240-420): compiled binding when present, else the ctypes implementation below."""
+    if _N is not None and _force_kernel == 0:
+        r = _N.fwd(q, k, v, out_, alibi_slopes_, p_dropout, softmax_scale, is_causal, window_size_left,
+                   window_size_right, return_softmax, gen_)
+        last_call_info._native_call()
+        return r
+    return _fwd_py(q, k, v, out_, alibi_slopes_, p_dropout, softmax_scale, is_causal, window_size_left,
+                   window_size_right, return_softmax, gen_)
+
+
+def _fwd_py(q, k, v, out_, alibi_slopes_, p_dropout, softmax_scale, is_causal, window_size_left,
+            window_size_right, return_softmax, gen_) -> List[torch.Tensor]:
     """mha_fwd (flash_api.cpp:240-420).  q (b,sq,h,d); k,v (b,sk,hk,d).
     Returns [out, q_padded, k_padded, v_padded, out_padded, softmax_lse, p, rng_state]."""
     _check_qkv(q, k, v)
@@ -231,6 +269,21 @@ def fwd(q, k, v, out_, alibi_slopes_, p_dropout, softmax_scale, is_causal, windo
 def varlen_fwd(q, k, v, out_, cu_seqlens_q, cu_seqlens_k, seqused_k, block_table_, alibi_slopes_,
                max_seqlen_q, max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal,
                window_size_left, window_size_right, return_softmax, gen_) -> List[torch.Tensor]:
+    """mha_varlen_fwd (flash_api.cpp:422-669): compiled binding when present, else the ctypes implementation below."""
+    if _N is not None and _force_kernel == 0:
+        r = _N.varlen_fwd(q, k, v, out_, cu_seqlens_q, cu_seqlens_k, seqused_k, block_table_, alibi_slopes_,
+                          max_seqlen_q, max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal,
+                          window_size_left, window_size_right, return_softmax, gen_)
+        last_call_info._native_call()
+        return r
+    return _varlen_fwd_py(q, k, v, out_, cu_seqlens_q, cu_seqlens_k, seqused_k, block_table_, alibi_slopes_,
+                          max_seqlen_q, max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal,
+                          window_size_left, window_size_right, return_softmax, gen_)
+
+
+def _varlen_fwd_py(q, k, v, out_, cu_seqlens_q, cu_seqlens_k, seqused_k, block_table_, alibi_slopes_,
+                   max_seqlen_q, max_seqlen_k, p_dropout, softmax_scale, zero_tensors, is_causal,
+                   window_size_left, window_size_right, return_softmax, gen_) -> List[torch.Tensor]:
     """mha_varlen_fwd (flash_api.cpp:422-669).  q (total_q,h,d); k,v (total_k,hk,d) or, with
     block_table (b,max_blocks), paged (num_blocks,page,hk,d).  softmax_lse is (b,h,max_seqlen_q)."""
     _check_qkv(q, k, v)
@@ -329,6 +382,12 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
     ``_fused_exchange`` (extension used by vllm_flash_attn.sharded): a _cabi.FaFusedExchange; with ``_kv_shard`` set the
     decode kernel then merges its splits, exchanges the merged rows with the peer GPUs and writes the FINAL out / lse
     itself (one launch per decode step)."""
+    if _N is not None and _force_kernel == 0 and _partial_buf is None and _kv_shard is None and _fused_exchange is None:
+        r = _N.fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_, cache_batch_idx_, block_table_,
+                           alibi_slopes_, out_, softmax_scale, is_causal, window_size_left, window_size_right,
+                           is_rotary_interleaved, num_splits)
+        last_call_info._native_call()
+        return r
     _check_qkv(q, kcache, vcache)
     dev = q.device
     _chk(q.dim() == 4 and kcache.dim() == 4 and vcache.dim() == 4, "q, kcache, vcache must be 4-D")
