@@ -583,7 +583,11 @@ def bench_c4(fa, ext, dev, world, rank, pk, iters=20):
             "prefill_part_frac_of_peak": flops / world / (t_pre * 1e-3) / 1e12 / pk["bf16_tflops"],
             "decode_part_frac_of_peak": nbytes / world / (t_dec * 1e-3) / 1e9 / pk["hbm_gbs"],
             "launches_per_call": launches, "collective": "none (heads independent)",
-            "parity_max_abs_vs_1gpu": parity, "parity_ok": (parity is not None and parity <= 1e-6) if rank == 0 else None}
+            # heads are independent, so the prefill rows are bit-identical to the unsharded call; the decode rows may
+            # differ by one bf16 rounding (4e-3 for |x| < 1): a shard with few KV heads splits its decode half along
+            # the context (fa_api.cu), the all-heads call on one GPU does not — a different fp32 summation tree
+            "parity_max_abs_vs_1gpu": parity, "parity_tolerance": 4e-3,
+            "parity_ok": (parity is not None and parity <= 4e-3) if rank == 0 else None}
 
 
 def bench_c5(fa, ext, dev, world, rank, pk, batch, ctx=131072, iters=30):

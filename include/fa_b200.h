@@ -50,13 +50,16 @@ enum {
 
 /* Sequence-sharded decode in ONE kernel per rank (fwd_kvcache with FaFwdParams.fused_exchange set): the decode
  * kernel's last CTA per (sequence, kv head) "unit" merges the unit's split-KV partials, pushes the merged fp32 rows
- * into every rank's receive area through peer-mapped pointers (NVLink stores), publishes the unit's call number,
- * waits for the peers' and writes the final (out, lse) — no separate combine or exchange launch, no NCCL call.  No
+ * into every rank's receive area through peer-mapped pointers (NVLink stores) as FLAGGED words — each fp32 value
+ * in one 64-bit word together with the unit's call number, so the data is its own arrival flag: one one-way trip, no
+ * system-scope fence, no separate flag — polls the peers' words and writes the final (out, lse): no separate combine or
+ * exchange launch, no NCCL call.  No
  * reference analogue (the reference has no multi-GPU path); the algebra is combine_attn_seqk_parallel's
  * (flash_fwd_kernel.h:1151-1221) applied to splits, then to ranks.  All areas live in one symmetric allocation per
  * rank, zeroed once, mapped into every process of the box (e.g. torch symmetric memory):
- *   recv  [2][world][max_units][unit_elems] fp32   receive area, double-buffered by the unit's call parity
- *   flags [world][max_units] uint32                flags[r][u] = call number of unit u last delivered by rank r
+ *   recv  [2][world][max_units][unit_elems] 64-bit words {fp32 value, uint32 call number}: receive area, double-
+ *                                                  buffered by the unit's call parity (8 bytes per value)
+ *   flags [world][max_units] uint32                reserved (the flagged words replaced the per-unit flags)
  *   state [max_units] uint32                       this rank's per-unit call numbers
  *   split_counters [max_units] int32               arrival counters of the in-kernel split merge (self-resetting)
  * Every rank must make the same sequence of calls (same b, h_k per call).  Slots are private to a unit, so the
@@ -69,7 +72,7 @@ typedef struct FaFusedExchange {
   int32_t* split_counters;       /* own */
   int32_t rank, world;           /* world <= FA_MAX_PEERS */
   int32_t max_units;             /* capacity: b*h_k of a call must not exceed it */
-  int64_t unit_elems;            /* fp32 per slot: >= seqlen_q*(h/h_k)*(d+1), multiple of 4 */
+  int64_t unit_elems;            /* values per slot (8 bytes each): >= seqlen_q*(h/h_k)*(d+1), multiple of 4 */
 } FaFusedExchange;
 
 typedef struct FaFwdParams {

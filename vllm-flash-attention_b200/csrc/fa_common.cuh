@@ -123,6 +123,15 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+// ---- flagged 16-byte lines (the "LL" form NCCL uses for small messages): two fp32 values, each packed with the call's
+// sequence number into one 64-bit word.  A naturally aligned 64-bit store is single-copy atomic, so the receiver that
+// sees the sequence number in a word also sees its value: the data is its own arrival flag, and a cross-GPU transfer
+// costs ONE one-way trip instead of data + system-scope release fence (a round trip) + flag (another one-way trip).
+__device__ __forceinline__ void st_flagged(float* line, float a, float b, uint32_t n) {
+  const unsigned long long x = (unsigned long long)__float_as_uint(a) | ((unsigned long long)n << 32);
+  const unsigned long long y = (unsigned long long)__float_as_uint(b) | ((unsigned long long)n << 32);
+  asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(line), "l"(x), "l"(y) : "memory");
+}
 #ifndef FA_XCHG_TIMEOUT_NS
 #define FA_XCHG_TIMEOUT_NS 120000000000ll   /* a peer may be late by a module load, a graph capture or a host stall; a MISSING peer still ends in a launch failure, not a hung GPU */
 #endif
@@ -135,6 +144,21 @@ __device__ __forceinline__ void wait_flag_sys(const unsigned* flag, unsigned n) 
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
     if (t1 - t0 > FA_XCHG_TIMEOUT_NS) __trap();
   }
+}
+// Poll one flagged line until both words carry sequence number n (bounded like wait_flag_sys).
+__device__ __forceinline__ float2 ld_flagged(const float* line, uint32_t n) {
+  unsigned long long x, y;
+  long long t0 = 0;
+  for (uint32_t spins = 0;; spins++) {
+    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "l"(line) : "memory");
+    if ((uint32_t)(x >> 32) == n && (uint32_t)(y >> 32) == n) break;
+    if ((spins & 1023u) == 1023u) {
+      long long now; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > FA_XCHG_TIMEOUT_NS) __trap();
+    }
+  }
+  return make_float2(__uint_as_float((uint32_t)x), __uint_as_float((uint32_t)y));
 }
 
 // ---------------------------------------------------------------------------------------

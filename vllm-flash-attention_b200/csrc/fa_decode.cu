@@ -363,42 +363,48 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
     // red[r][0..D) = this rank's normalised fp32 O rows of the unit, row_lse[r] = natural-log LSE (-inf: no key)
 
     if (p.xchg_world > 0) {
-      // d. exchange (see fa_exchange.cu for the two-kernel form of the same protocol): call number n of THIS unit;
-      // slot (n & 1, source rank, unit) of every rank's receive area is private to the unit, so units whose call
-      // numbers differ (varying batch sizes) never touch each other's data; a rank cannot run two calls ahead of a
-      // peer for the same unit (its call n+1 needs the peer's flag n+1, sent after the peer finished call n).
+      // d. exchange: call number n of THIS unit; slot (n & 1, source rank, unit) of every rank's receive area is
+      // private to the unit, so units whose call numbers differ (varying batch sizes) never touch each other's data;
+      // a rank cannot run two calls ahead of a peer for the same unit (its call n+1 needs the peer's lines of call
+      // n+1, sent after the peer finished call n).  The rows travel as FLAGGED LINES (fa_common.cuh: two fp32, each
+      // in one 64-bit word with n): the data is its own arrival flag, so a rank's rows cost the peers one one-way trip —
+      // no system-scope release fence (a round trip over NVSwitch) and no separate flag behind it.
       if (tid == 0) s_n = p.xchg_state[unit] + 1u;
       __syncthreads();
       const unsigned n = s_n;
       const int W = p.xchg_world;
-      auto slot = [&](int src) { return ((int64_t)((n & 1u) * W + src) * p.xchg_max_units + unit) * p.xchg_unit_elems; };
+      constexpr int LPR = D / 2;                                     // lines per row
+      const int o_lines = Rw * LPR, all_lines = o_lines + (Rw + 1) / 2;   // O rows, then the LSEs two per line
+      // slot base in floats: a slot holds unit_elems values = unit_elems 64-bit words
+      auto slot = [&](int src) { return ((int64_t)((n & 1u) * W + src) * p.xchg_max_units + unit) * p.xchg_unit_elems * 2; };
       const int64_t mine = slot(p.xchg_rank);
-      for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
-        const int r = idx / (D / 4), c4 = idx % (D / 4);
-        const float4 x = *reinterpret_cast<const float4*>(red + r * Cfg::RED_STRIDE + c4 * 4);
-        for (int w = 0; w < W; w++) *reinterpret_cast<float4*>(p.xchg_recv[w] + mine + r * D + c4 * 4) = x;
+      for (int idx = tid; idx < all_lines; idx += NW * 32) {
+        float a, b;
+        if (idx < o_lines) {
+          const int r = idx / LPR, c2 = idx - r * LPR;
+          const float2 x = *reinterpret_cast<const float2*>(red + r * Cfg::RED_STRIDE + 2 * c2);
+          a = x.x; b = x.y;
+        } else {
+          const int r = 2 * (idx - o_lines);
+          a = row_lse[r]; b = r + 1 < Rw ? row_lse[r + 1] : 0.f;
+        }
+        for (int w = 0; w < W; w++)
+          if (w != p.xchg_rank) st_flagged(p.xchg_recv[w] + mine + (int64_t)idx * 4, a, b, n);
       }
-      for (int r = tid; r < Rw; r += NW * 32) {
-        const float l = row_lse[r];
-        for (int w = 0; w < W; w++) p.xchg_recv[w][mine + Rw * D + r] = l;
-      }
-      // One system-scope release per flag: the CTA barrier orders every thread's row stores before the flag threads,
-      // and st.release.sys (fence + store) by a flag thread is cumulative over what it observed through the barrier —
-      // a separate __threadfence_system() by all threads before it would be a second fence round trip in series.
-      __syncthreads();
-      if (tid < W) {
-        st_release_sys(p.xchg_flags[tid] + p.xchg_rank * p.xchg_max_units + unit, n);
-        wait_flag_sys(p.xchg_flags[p.xchg_rank] + tid * p.xchg_max_units + unit, n);
-      }
-      if (tid == 0) p.xchg_state[unit] = n;
-      __syncthreads();
-      // e. merge the ranks' rows: one warp per row
+      __syncthreads();                                                 // every thread has read red / row_lse for the push
+      // e. merge the ranks' rows as they arrive: one warp per row; own rows straight from shared memory, fixed rank
+      // order (every rank computes the same sums)
       const float* base = p.xchg_recv[p.xchg_rank];
       for (int r = warp; r < Rw; r += NW) {
+        float my_ls = -INFINITY;
+        if (lane < W) {
+          if (lane == p.xchg_rank) my_ls = row_lse[r];
+          else { const float2 t = ld_flagged(base + slot(lane) + (int64_t)(o_lines + (r >> 1)) * 4, n); my_ls = (r & 1) ? t.y : t.x; }
+        }
         float ls[FA_KP_MAX_PEERS], mx = -INFINITY;
 #pragma unroll
         for (int w = 0; w < FA_KP_MAX_PEERS; w++) {
-          ls[w] = w < W ? __ldcg(base + slot(w) + Rw * D + r) : -INFINITY;
+          ls[w] = __shfl_sync(0xffffffffu, my_ls, w);                  // lanes >= W hold -inf
           mx = fmaxf(mx, ls[w]);
         }
         const bool empty = mx == -INFINITY;
@@ -409,19 +415,22 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
         float wg[FA_KP_MAX_PEERS];
 #pragma unroll
         for (int w = 0; w < FA_KP_MAX_PEERS; w++) wg[w] = empty ? 0.f : expf(ls[w] - lse);
-        for (int col = lane * 4; col < D; col += 128) {
-          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int c2 = lane; c2 < LPR; c2 += 32) {
+          float2 acc = make_float2(0.f, 0.f);
+          float2* own = reinterpret_cast<float2*>(red + r * Cfg::RED_STRIDE + 2 * c2);
 #pragma unroll
           for (int w = 0; w < FA_KP_MAX_PEERS; w++) {
             if (w < W) {
-              const float4 x = __ldcg(reinterpret_cast<const float4*>(base + slot(w) + r * D + col));
-              acc.x += wg[w] * x.x; acc.y += wg[w] * x.y; acc.z += wg[w] * x.z; acc.w += wg[w] * x.w;
+              const float2 x = w == p.xchg_rank ? *own : ld_flagged(base + slot(w) + (int64_t)(r * LPR + c2) * 4, n);
+              acc.x += wg[w] * x.x; acc.y += wg[w] * x.y;
             }
           }
-          *reinterpret_cast<float4*>(red + r * Cfg::RED_STRIDE + col) = acc;
+          *own = acc;
         }
+        __syncwarp();
         if (lane == 0) row_lse[r] = lse;
       }
+      if (tid == 0) p.xchg_state[unit] = n;
       __syncthreads();
     }
 

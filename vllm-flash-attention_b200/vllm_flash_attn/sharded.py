@@ -135,7 +135,8 @@ class PeerExchange:
         # areas of the one-kernel path (include/fa_b200.h, FaFusedExchange); absent when fused_units == 0
         self.fused_units, self.fused_unit_elems = int(fused_units), (int(fused_unit_elems) + 3) // 4 * 4
         self.off_frecv = (self.off_local + self.record + 3) // 4 * 4
-        self.off_fflags = self.off_frecv + 2 * self.world * self.fused_units * self.fused_unit_elems
+        # receive area of the one-kernel path: flagged lines, 8 bytes per fp32 value (value + the call's sequence number)
+        self.off_fflags = self.off_frecv + 2 * (2 * self.world * self.fused_units * self.fused_unit_elems)
         self.off_fstate = self.off_fflags + 8 * self.fused_units
         self.off_fcount = self.off_fstate + self.fused_units
         total = self.off_fcount + self.fused_units
