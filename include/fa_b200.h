@@ -182,6 +182,12 @@ int fa_b200_fwd(FaFwdParams* p, void* stream);
 int fa_b200_varlen_fwd(FaFwdParams* p, void* stream);
 int fa_b200_fwd_kvcache(FaFwdParams* p, void* stream);
 
+/* Will fa_b200_fwd_kvcache append the call's new K/V rows (knew / vnew, with rotary on K and q when rotary_cos/sin are
+ * set) INSIDE its own kernel, as the reference's split kernel does (flash_fwd_kernel.h:672-824)?  1 = yes: pass
+ * knew / vnew / rotary_* / seqlen_knew to fa_b200_fwd_kvcache directly (one launch, the rotated q never exists in
+ * memory); 0 = no (not a decode shape, sliding window, or kv_shard): run fa_b200_append_kv first; < 0 = invalid. */
+int fa_b200_fused_append_supported(const FaFwdParams* p);
+
 /* Append the new K/V rows of a fwd_kvcache call into the (paged) cache at cache_seqlens[b]+i, with
  * rotary embedding on K (and on q, written to p->workspace as (b,seqlen_q,h,d)) when rotary_cos/sin
  * are set — the append half of the reference's fused path (flash_fwd_kernel.h:672-824).  The caller

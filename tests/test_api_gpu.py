@@ -133,13 +133,19 @@ def test_combine_entry_point():
     assert (lse.cpu()[fin] - lc[fin]).abs().max() < 1e-4
 
 
+@pytest.mark.parametrize("mode", ["fused", "two_step"])
 @pytest.mark.parametrize("paged", [False, True])
 @pytest.mark.parametrize("interleaved", [True, False])
 @pytest.mark.parametrize("rotary_frac", [0.0, 0.5, 1.0])
-def test_append_kv_and_rotary(paged, interleaved, rotary_frac):
+def test_append_kv_and_rotary(paged, interleaved, rotary_frac, mode, monkeypatch):
     """tests/test_flash_attn.py:1944-2074: new k/v are appended at cache_seqlens (rotary applied),
-    cache contents are checked afterwards, output matches attention over the updated cache."""
+    cache contents are checked afterwards, output matches attention over the updated cache.  `fused`: the decode
+    kernel appends and rotates itself (the reference's fused path, flash_fwd_kernel.h:672-824); `two_step`: the
+    stand-alone append kernel runs first (what non-decode shapes use)."""
     import vllm_flash_attn as fa
+    from vllm_flash_attn import vllm_flash_attn_2_cuda as ext
+    if mode == "two_step":
+        monkeypatch.setattr(ext, "_two_step_append", True)
     torch.manual_seed(0)
     dev, dt = "cuda", torch.float16
     b, sq, sk, skn, h, hk, d = 2, 3, 160, 3, 4, 2, 64
@@ -190,6 +196,77 @@ def test_append_kv_and_rotary(paged, interleaved, rotary_frac):
     ref32, _ = orc.attention_ref(q_ro, kfull, vfull, None, kpm, causal=True)
     pt, _ = orc.attention_ref(q_ro, kfull, vfull, None, kpm, causal=True, upcast=False, reorder_ops=True)
     assert (out.float() - ref32.float()).abs().max() <= 3 * (pt.float() - ref32.float()).abs().max() + 1e-5
+
+
+@pytest.mark.parametrize("sq,skn,causal", [(1, 1, True), (2, 2, True), (1, 3, False)])
+def test_fused_append_long_context_with_splits(sq, skn, causal, monkeypatch):
+    """In-kernel append on a split decode: the new rows are written by the ONE split CTA whose chunk range holds them
+    (here the last split, or — for the length that ends on a chunk boundary — a CTA that starts with them), every other
+    CTA never touches them.  Output, LSE and the cache afterwards are bit-identical to the two-step path (same fp32
+    rotation, same attention kernel over the same cache contents); q and the new k/v themselves are left untouched."""
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import vllm_flash_attn_2_cuda as ext
+    torch.manual_seed(5)
+    dev, dt, page = "cuda", torch.bfloat16, 16
+    b, h, hk, d, ctx = 3, 16, 2, 128, 8192
+    mb = ctx // page
+    lens = torch.tensor([5000, ctx - skn, 4096], dtype=torch.int32, device=dev)      # mid-page, cache exactly filled, chunk boundary
+    kc0 = torch.randn(b * mb, page, hk, d, device=dev, dtype=dt); vc0 = torch.randn_like(kc0)
+    bt = torch.randperm(b * mb, device=dev).to(torch.int32).view(b, mb).contiguous()
+    q = torch.randn(b, sq, h, d, device=dev, dtype=dt); q_keep = q.clone()
+    kn = torch.randn(b, skn, hk, d, device=dev, dtype=dt); vn = torch.randn_like(kn); kn_keep = kn.clone()
+    ang = torch.rand(ctx, d // 2, device=dev) * 2 * math.pi
+    cos, sin = torch.cos(ang).to(dt), torch.sin(ang).to(dt)
+
+    def run(two_step):
+        monkeypatch.setattr(ext, "_two_step_append", two_step)
+        kc, vc = kc0.clone(), vc0.clone()
+        o, l = fa.flash_attn_with_kvcache(q, kc, vc, kn, vn, rotary_cos=cos, rotary_sin=sin, cache_seqlens=lens, block_table=bt,
+                                          causal=causal, rotary_interleaved=False, return_softmax_lse=True)
+        return o, l, kc, vc, dict(ext.last_call_info)
+    of, lf, kf, vf, info_f = run(False)
+    ot, lt, kt, vt, info_t = run(True)
+    assert info_f["kernel_used"] == 3 and info_f["num_splits"] > 1 and info_f == info_t, (info_f, info_t)
+    assert torch.equal(kf, kt) and torch.equal(vf, vt) and not torch.equal(kf, kc0)
+    assert torch.equal(of, ot) and torch.equal(lf, lt)
+    assert torch.equal(q, q_keep) and torch.equal(kn, kn_keep)
+
+
+def test_append_on_a_prefill_shape_takes_the_two_step_path():
+    """64 new tokens per sequence against a cache (chunked prefill through flash_attn_with_kvcache): not a decode shape,
+    so fa_b200_fused_append_supported says no and the bindings run the append kernel first; a sliding window does the
+    same on a decode shape.  Both host bindings, same results."""
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import _cabi
+    from vllm_flash_attn import vllm_flash_attn_2_cuda as ext
+    torch.manual_seed(6)
+    dev, dt = "cuda", torch.bfloat16
+    b, sq, h, hk, d, sk = 2, 64, 8, 2, 128, 512
+    q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
+    kn = torch.randn(b, sq, hk, d, device=dev, dtype=dt); vn = torch.randn_like(kn)
+    kc0 = torch.randn(b, sk, hk, d, device=dev, dtype=dt); vc0 = torch.randn_like(kc0)
+    lens = torch.tensor([300, 17], dtype=torch.int32, device=dev)
+    outs = []
+    for native in (True, False):
+        if native and ext._NATIVE is None:
+            continue
+        saved = ext._N
+        ext._N = ext._NATIVE if native else None
+        try:
+            for window in ((-1, -1), (100, 0)):
+                qq = q if window == (-1, -1) else q[:, :1]
+                kk, vv = (kn, vn) if window == (-1, -1) else (kn[:, :1], vn[:, :1])
+                kc, vc = kc0.clone(), vc0.clone()
+                o = fa.flash_attn_with_kvcache(qq, kc, vc, kk, vv, cache_seqlens=lens, causal=True, window_size=window)
+                full_k, full_v = kc0.clone(), vc0.clone()
+                for i in range(b):
+                    L = int(lens[i]); full_k[i, L:L + kk.shape[1]] = kk[i]; full_v[i, L:L + kk.shape[1]] = vv[i]
+                assert torch.equal(kc, full_k) and torch.equal(vc, full_v)
+                outs.append((native, window, o))
+        finally:
+            ext._N = saved
+    if len(outs) == 4:
+        assert torch.equal(outs[0][2], outs[2][2]) and torch.equal(outs[1][2], outs[3][2])
 
 
 def test_cache_batch_idx_and_seqlen_k_zero():

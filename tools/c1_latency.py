@@ -13,6 +13,11 @@ page, mb, b = 16, 64, 16
 kc = torch.randn(b * mb, page, 8, 128, device="cuda", dtype=torch.bfloat16); vc = torch.randn_like(kc)
 bt = torch.randperm(b * mb, device="cuda").to(torch.int32).view(b, mb).contiguous()
 qd = torch.randn(b, 1, 32, 128, device="cuda", dtype=torch.bfloat16); cl = torch.full((b,), 1000, dtype=torch.int32, device="cuda")
+import math
+kn = torch.randn(b, 1, 8, 128, device="cuda", dtype=torch.bfloat16); vn = torch.randn_like(kn)
+ang = torch.rand(mb * page, 64, device="cuda") * 2 * math.pi
+cos, sin = torch.cos(ang).to(torch.bfloat16), torch.sin(ang).to(torch.bfloat16)
+append = lambda: fa.flash_attn_with_kvcache(qd, kc, vc, kn, vn, rotary_cos=cos, rotary_sin=sin, cache_seqlens=cl, block_table=bt, causal=True)
 calls = {"c1_flash_attn_func": lambda: fa.flash_attn_func(q, k, v),
          "decode_step_flash_attn_with_kvcache": lambda: fa.flash_attn_with_kvcache(qd, kc, vc, cache_seqlens=cl, block_table=bt, causal=True)}
 
@@ -49,6 +54,14 @@ for name, f in calls.items():
         row[binding + "_host_enqueue_us"] = round(enq, 2); row[binding + "_wall_us"] = round(wall, 2)
     ext._N = native
     print(json.dumps(row), flush=True)
+# decode step that also appends the step's k/v with rotary: in-kernel append (one launch) vs the stand-alone append kernel first
+for two_step in (False, True):
+    ext._two_step_append = two_step
+    enq, wall = host_us(append)
+    print(json.dumps({"call": "decode_step_with_append_and_rotary", "append": "stand-alone kernel first" if two_step else "in the decode kernel",
+                      "binding": "ctypes" if two_step or native is None else "pybind11", "device_us": round(device_us(append), 2),
+                      "host_enqueue_us": round(enq, 2), "wall_us": round(wall, 2)}), flush=True)
+ext._two_step_append = False
 if "--profile" in sys.argv:
     import cProfile, pstats
     pr = cProfile.Profile(); pr.enable()

@@ -139,8 +139,25 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
     FA_CHECK(a->max_blocks_per_seq > 0, "block_table must have at least one column");
   }
   if (a->alibi_slopes == nullptr) FA_CHECK(a->alibi_slopes_batch_stride == 0, "alibi stride without slopes");
-  FA_CHECK(a->knew == nullptr && a->vnew == nullptr && a->rotary_cos == nullptr,
-           "append-KV / rotary are applied by fa_b200_append_kv before the attention call");
+  // New K/V rows given to the attention call itself: appended (and rotated, with q) INSIDE the decode kernel — the
+  // reference's fused path (flash_fwd_kernel.h:672-824).  Only fwd_kvcache, only when the call runs on the decode
+  // kernel (checked below, fa_b200_fused_append_supported tells beforehand); otherwise the caller runs
+  // fa_b200_append_kv first and passes seqlen_knew alone.
+  const bool fused_append = a->knew != nullptr;
+  if (fused_append) {
+    FA_CHECK(op == OP_KVCACHE, "knew / vnew are only valid for fwd_kvcache");
+    FA_CHECK(a->vnew != nullptr, "key and value must be passed together");
+    FA_CHECK(a->cu_seqlens_k != nullptr, "seqlens_k must be passed if key/value are passed");
+    FA_CHECK(a->seqlen_knew > 0, "seqlen_knew must be positive when knew is given");
+    if (a->rotary_cos) {
+      FA_CHECK(a->rotary_sin != nullptr, "If rotary cos is provided, rotary sin must also be provided");
+      FA_CHECK(a->rotary_dim <= a->d, "rotary_dim must be <= headdim");
+      FA_CHECK(a->rotary_dim % 16 == 0, "Only rotary dimensions divisible by 16 are currently supported");
+    }
+  } else {
+    FA_CHECK(a->vnew == nullptr && a->rotary_cos == nullptr,
+             "rotary / vnew without knew: append-KV and rotary are applied by fa_b200_append_kv or by passing knew to fwd_kvcache");
+  }
   FA_CHECK(a->seqlen_knew >= 0 && (a->seqlen_knew == 0 || op == OP_KVCACHE), "seqlen_knew is only valid for fwd_kvcache");
 
   KParams& k = pl->k;
@@ -227,6 +244,17 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
       // kernel (one CTA per KV head, K/V read once per group) by a second launch over the same batch.
       if (op == OP_VARLEN && decode_supported(a->d, k.group)) pl->decode_rows = a->d <= 128 ? 32 : 16;   // the decode kernel's row capacity
     } else kernel = FA_KERNEL_TILE;
+  }
+  if (fused_append) {
+    FA_CHECK(kernel == FA_KERNEL_DECODE && !k.is_local && a->kv_shard_len == 0,
+             "in-kernel append needs a decode shape (seqlen_q*(h/h_k) <= 32; 16 above d = 128), no sliding window and no kv_shard: "
+             "run fa_b200_append_kv first and pass seqlen_knew alone (fa_b200_fused_append_supported tells beforehand)");
+    k.knew = a->knew; k.vnew = a->vnew;
+    k.knew_batch_stride = a->knew_batch_stride; k.knew_row_stride = a->knew_row_stride; k.knew_head_stride = a->knew_head_stride;
+    k.vnew_batch_stride = a->vnew_batch_stride; k.vnew_row_stride = a->vnew_row_stride; k.vnew_head_stride = a->vnew_head_stride;
+    k.rotary_cos = a->rotary_cos; k.rotary_sin = a->rotary_sin;
+    k.rotary_dim = a->rotary_cos ? a->rotary_dim : 0; k.seqlen_ro = a->seqlen_ro; k.rotary_interleaved = a->is_rotary_interleaved;
+    k.rot_by_qpos = (k.is_causal || k.is_local) ? 1 : 0;       // q row i rotated at cache_len + i (flash_fwd_kernel.h:794)
   }
   if (fx) FA_CHECK(kernel == FA_KERNEL_DECODE, "fused_exchange: the call must have a decode shape (seqlen_q*(h/h_k) <= 32; 16 above d = 128)");
   if (kernel == FA_KERNEL_DECODE) FA_CHECK(decode_supported(a->d, rows), "decode kernel: d/rows not supported");
@@ -499,6 +527,19 @@ extern "C" int fa_b200_append_kv(FaFwdParams* a, void* stream) {
   cudaError_t e = launch_append(p, a->is_bf16 != 0, (cudaStream_t)stream);
   if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in append kernel launch: %s", cudaGetErrorString(e));
   return FA_OK;
+}
+
+// Will fa_b200_fwd_kvcache append p->knew / p->vnew (and apply rotary) inside its own kernel?  1 = yes (pass them to
+// fwd_kvcache directly: one launch), 0 = no (run fa_b200_append_kv first), negative = invalid arguments.
+extern "C" int fa_b200_fused_append_supported(const FaFwdParams* a) {
+  g_err[0] = 0;
+  FA_CHECK(a != nullptr, "params is NULL");
+  FaFwdParams t = *a;
+  t.knew = t.vnew = t.rotary_cos = t.rotary_sin = nullptr;       // plan the attention call alone
+  Plan pl;
+  const int rc = make_plan(&t, OP_KVCACHE, &pl);
+  if (rc != FA_OK) return rc;
+  return pl.kernel == FA_KERNEL_DECODE && !pl.k.is_local && a->kv_shard_len == 0 ? 1 : 0;
 }
 
 // Sequence-sharded decode: push + wait + LSE-combine across the GPUs of one box (csrc/fa_exchange.cu).

@@ -50,6 +50,12 @@ struct KParams {
   unsigned* xchg_state;                         // this rank's per-unit call numbers
   int xchg_rank, xchg_world, xchg_max_units;    // xchg_world == 0: no exchange
   int64_t xchg_unit_elems;                      // fp32 per (parity, source rank, unit) slot
+  // ---- decode kernel: in-kernel append of the call's new K/V rows (+ rotary on K and q), fa_decode.cu ----
+  const void* knew; const void* vnew;           // (b, seqlen_knew, h_k, d) or NULL: rows are already in the cache
+  int64_t knew_batch_stride, knew_row_stride, knew_head_stride;
+  int64_t vnew_batch_stride, vnew_row_stride, vnew_head_stride;
+  const void* rotary_cos; const void* rotary_sin;   // (seqlen_ro, rotary_dim / 2) or NULL
+  int rotary_dim, seqlen_ro, rotary_interleaved, rot_by_qpos;
 };
 constexpr int FA_KP_MAX_PEERS = 8;
 

@@ -17,6 +17,7 @@
 #include "fa_common.cuh"
 #include "fa_warp_attn.cuh"
 #include "fa_launch.h"
+#include "fa_rotary.cuh"
 
 namespace fa {
 
@@ -65,8 +66,63 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
   const int c_begin = c_lo + split * per_split;
   const int c_end = min(c_hi, c_begin + per_split);
 
+  // ---- in-kernel append (flash_fwd_kernel.h:672-824): the call's new K/V rows, rotated, go into the cache here instead
+  // of in a launch of their own.  Row L + i (L = length before the call) is written by the ONE CTA of this KV head whose
+  // chunk range holds it — one CTA per (sequence, kv head, split), so no two CTAs write the same row (the reference
+  // documents a benign race between the query heads of a group, :678-680) — made visible device-wide, and only then do
+  // this CTA's warps start streaming chunks; every other CTA never reads those rows.
+  if (p.knew != nullptr) {
+    const int L = sk - p.seqlen_knew;
+    const int r_lo = max(L, c_begin * 16), r_hi = min(sk, c_end * 16);
+    const int half = p.rotary_dim / 2;
+    for (int pos = r_lo + warp; pos < r_hi; pos += NW) {
+      const int i = pos - L;
+      int64_t koff, voff;
+      if (p.block_table) {
+        const int pg = min(pos / p.page_block_size, p.max_blocks_per_seq - 1);
+        const int blk = p.block_table[(int64_t)bidb * p.block_table_batch_stride + pg];
+        const int in_page = pos - (pos / p.page_block_size) * p.page_block_size;
+        koff = (int64_t)blk * p.k_batch_stride + (int64_t)in_page * p.k_row_stride;
+        voff = (int64_t)blk * p.v_batch_stride + (int64_t)in_page * p.v_row_stride;
+      } else {
+        if (pos >= p.seqlen_k) continue;          // cache full: the reference would write out of bounds
+        koff = si.k_off + (int64_t)pos * p.k_row_stride;
+        voff = si.v_off + (int64_t)pos * p.v_row_stride;
+      }
+      const T* ksrc = reinterpret_cast<const T*>(p.knew) + (int64_t)bidb * p.knew_batch_stride + (int64_t)i * p.knew_row_stride + (int64_t)kvh * p.knew_head_stride;
+      const T* vsrc = reinterpret_cast<const T*>(p.vnew) + (int64_t)bidb * p.vnew_batch_stride + (int64_t)i * p.vnew_row_stride + (int64_t)kvh * p.vnew_head_stride;
+      T* kdst = const_cast<T*>(reinterpret_cast<const T*>(p.k)) + koff + (int64_t)kvh * p.k_head_stride;
+      T* vdst = const_cast<T*>(reinterpret_cast<const T*>(p.v)) + voff + (int64_t)kvh * p.v_head_stride;
+      const int rp = min(pos, max(p.seqlen_ro - 1, 0));
+      rotate_row<T>(ksrc, kdst, D, p.rotary_cos ? p.rotary_dim : 0, p.rotary_interleaved != 0,
+                    reinterpret_cast<const T*>(p.rotary_cos) + (int64_t)rp * half,
+                    reinterpret_cast<const T*>(p.rotary_sin) + (int64_t)rp * half, lane, 32);
+      rotate_row<T>(vsrc, vdst, D, 0, true, nullptr, nullptr, lane, 32);
+    }
+    if (r_lo < r_hi) __threadfence();
+    __syncthreads();
+  }
+
   // ---- Q: gather the packed rows into shared memory (zero rows beyond R) ----
-  {
+  if (p.rotary_cos != nullptr) {
+    // rotary on q (rotary.h:19-145): row qpos at position L (+ qpos under a causal / local mask), rotated on its way
+    // into the tile — the rotated q never exists in global memory
+    const T* qb = reinterpret_cast<const T*>(p.q) + si.q_off;
+    const int L = sk - p.seqlen_knew, half = p.rotary_dim / 2;
+    for (int r = warp; r < ROWS; r += NW) {
+      if (r < R) {
+        const int qpos = r / g, hg = r - qpos * g;
+        const int rp = min(L + (p.rot_by_qpos ? qpos : 0), max(p.seqlen_ro - 1, 0));
+        const T* src = qb + (int64_t)qpos * p.q_row_stride + (int64_t)(kvh * g + hg) * p.q_head_stride;
+        rotate_row_to<T>(src, [&](int c) { return reinterpret_cast<T*>(q_sm + swz<D>(r, c)); }, D, p.rotary_dim, p.rotary_interleaved != 0,
+                         reinterpret_cast<const T*>(p.rotary_cos) + (int64_t)rp * half,
+                         reinterpret_cast<const T*>(p.rotary_sin) + (int64_t)rp * half, lane, 32);
+      } else {
+        for (int c = lane; c < CPR; c += 32) *reinterpret_cast<uint4*>(q_sm + swz<D>(r, c)) = make_uint4(0, 0, 0, 0);
+      }
+    }
+    cp_async_commit();      // (empty) keeps the group count of the waits below
+  } else {
     const T* qb = reinterpret_cast<const T*>(p.q) + si.q_off;
     for (int idx = threadIdx.x; idx < ROWS * CPR; idx += NW * 32) {
       int r = idx / CPR, c = idx % CPR;

@@ -342,15 +342,23 @@ std::vector<at::Tensor> fwd_kvcache(at::Tensor& q, const at::Tensor& kcache, con
       TORCH_CHECK(rs.sizes() == rc.sizes(), "rotary_sin shape mismatch");
       P.rotary_cos = rc.data_ptr(); P.rotary_sin = rs.data_ptr();
       P.rotary_dim = (int)rd; P.seqlen_ro = (int)rc.size(0); P.is_rotary_interleaved = is_rotary_interleaved;
-      q_rot = torch::empty({b, sq, h, d}, q.options());
-      P.workspace = q_rot.data_ptr(); P.workspace_bytes = (size_t)q_rot.numel() * 2;
     }
-    ok(fa_b200_append_kv(&P, at::cuda::getCurrentCUDAStream(q.get_device()).stream()));
-    P.knew = P.vnew = P.rotary_cos = P.rotary_sin = nullptr;
-    P.workspace = nullptr; P.workspace_bytes = 0;
-    if (q_rot.defined()) {
-      P.q = q_rot.data_ptr();
-      P.q_batch_stride = q_rot.stride(0); P.q_row_stride = q_rot.stride(1); P.q_head_stride = q_rot.stride(2);
+    const int fused = fa_b200_fused_append_supported(&P);
+    TORCH_CHECK(fused >= 0, fa_b200_last_error());
+    if (!fused) {
+      // not a decode shape (or a sliding window): the stand-alone append kernel first, then attention over the grown
+      // cache with the rotated q.  Otherwise knew / vnew / rotary stay in the block and the decode kernel does it all.
+      if (rotary_cos_.has_value()) {
+        q_rot = torch::empty({b, sq, h, d}, q.options());
+        P.workspace = q_rot.data_ptr(); P.workspace_bytes = (size_t)q_rot.numel() * 2;
+      }
+      ok(fa_b200_append_kv(&P, at::cuda::getCurrentCUDAStream(q.get_device()).stream()));
+      P.knew = P.vnew = P.rotary_cos = P.rotary_sin = nullptr;
+      P.workspace = nullptr; P.workspace_bytes = 0;
+      if (q_rot.defined()) {
+        P.q = q_rot.data_ptr();
+        P.q_batch_stride = q_rot.stride(0); P.q_row_stride = q_rot.stride(1); P.q_head_stride = q_rot.stride(2);
+      }
     }
   } else {
     TORCH_CHECK(!rotary_cos_.has_value(), "rotary embedding requires new key/value (reference applies it in the append path)");

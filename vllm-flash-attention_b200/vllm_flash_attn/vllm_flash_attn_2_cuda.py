@@ -27,6 +27,7 @@ from . import _cabi
 from ._cabi import FaFwdParams, OP_FWD, OP_KVCACHE, OP_VARLEN, check, lib
 
 _force_kernel = 0          # tests: _cabi.FA_KERNEL_* to pin a kernel family
+_two_step_append = False   # tests: always run the stand-alone append kernel (ctypes path only)
 
 try:
     from . import _fa_torch as _N        # compiled host binding (optional; same library underneath)
@@ -382,7 +383,8 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
     ``_fused_exchange`` (extension used by vllm_flash_attn.sharded): a _cabi.FaFusedExchange; with ``_kv_shard`` set the
     decode kernel then merges its splits, exchanges the merged rows with the peer GPUs and writes the FINAL out / lse
     itself (one launch per decode step)."""
-    if _N is not None and _force_kernel == 0 and _partial_buf is None and _kv_shard is None and _fused_exchange is None:
+    if (_N is not None and _force_kernel == 0 and not _two_step_append and _partial_buf is None and _kv_shard is None
+            and _fused_exchange is None):
         r = _N.fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_, cache_batch_idx_, block_table_,
                            alibi_slopes_, out_, softmax_scale, is_causal, window_size_left, window_size_right,
                            is_rotary_interleaved, num_splits)
@@ -494,14 +496,23 @@ def fwd_kvcache(q, kcache, vcache, k_, v_, seqlens_k_, rotary_cos_, rotary_sin_,
                 P.rotary_cos, P.rotary_sin = rotary_cos_.data_ptr(), rotary_sin_.data_ptr()
                 P.rotary_dim, P.seqlen_ro = rd, rotary_cos_.shape[0]
                 P.is_rotary_interleaved = int(is_rotary_interleaved)
-                q_rot = torch.empty((b, sq, h, d), dtype=q.dtype, device=dev)
-                P.workspace, P.workspace_bytes = q_rot.data_ptr(), q_rot.numel() * 2
-            check(lib.fa_b200_append_kv(C.byref(P), _stream(dev)))
-            P.knew = P.vnew = P.rotary_cos = P.rotary_sin = None
-            P.workspace, P.workspace_bytes = None, 0
-            if q_rot is not None:
-                P.q = q_rot.data_ptr()
-                P.q_batch_stride, P.q_row_stride, P.q_head_stride = q_rot.stride(0), q_rot.stride(1), q_rot.stride(2)
+            P.force_kernel = _force_kernel
+            fused = lib.fa_b200_fused_append_supported(C.byref(P)) if not _two_step_append else 0
+            if fused < 0:
+                check(fused)
+            if not fused:
+                # not a decode shape (or a sliding window): the stand-alone append kernel first, then attention over
+                # the grown cache with the rotated q
+                if rotary_cos_ is not None:
+                    q_rot = torch.empty((b, sq, h, d), dtype=q.dtype, device=dev)
+                    P.workspace, P.workspace_bytes = q_rot.data_ptr(), q_rot.numel() * 2
+                check(lib.fa_b200_append_kv(C.byref(P), _stream(dev)))
+                P.knew = P.vnew = P.rotary_cos = P.rotary_sin = None
+                P.workspace, P.workspace_bytes = None, 0
+                if q_rot is not None:
+                    P.q = q_rot.data_ptr()
+                    P.q_batch_stride, P.q_row_stride, P.q_head_stride = q_rot.stride(0), q_rot.stride(1), q_rot.stride(2)
+            # else: knew / vnew / rotary stay in the block — the decode kernel appends and rotates itself (one launch)
         else:
             _chk(rotary_cos_ is None, "rotary embedding requires new key/value (reference applies it in the append path)")
         _run(P, OP_KVCACHE, lib.fa_b200_fwd_kvcache, dev)
