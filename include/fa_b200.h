@@ -207,6 +207,16 @@ int fa_b200_append_kv(FaFwdParams* p, void* stream);
 #define FA_B200_STATIC_SCRATCH_BYTES (4u << 20)
 int fa_b200_fwd_kvcache_static_scratch(FaFwdParams* p, void* stream);
 
+/* Cache writer of the caller's side (no counterpart in the reference repository; vLLM: reshape_and_cache_flash, SURVEY 8f
+ * rank 4): row t of key / value, (num_tokens, h_k, d) fp16 or bf16 with the given element strides, is copied to
+ * cache[slot / page][slot % page] with slot = slot_mapping[t] (int64, device); negative slots are skipped.  The caches are
+ * (num_blocks, page_block_size, h_k, d) with the given strides — the layout the three ops read. */
+int fa_b200_reshape_and_cache(const void* key, const void* value, void* kcache, void* vcache, const int64_t* slot_mapping,
+                              int num_tokens, int h_k, int d, int page_block_size, int64_t num_blocks,
+                              int64_t key_token_stride, int64_t key_head_stride, int64_t value_token_stride, int64_t value_head_stride,
+                              int64_t k_batch_stride, int64_t k_row_stride, int64_t k_head_stride,
+                              int64_t v_batch_stride, int64_t v_row_stride, int64_t v_head_stride, void* stream);
+
 /* Merge `n` partial results into o (rows,d) + lse (rows): lse = logsumexp_s lse_s,
  * o = sum_s exp(lse_s-lse) o_s — the algebra of combine_attn_seqk_parallel
  * (flash_fwd_kernel.h:1092-1250); used for the in-GPU split-KV merge and for the cross-GPU

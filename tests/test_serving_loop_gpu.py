@@ -28,11 +28,17 @@ def test_prefill_then_graph_captured_decode_loop():
     # ---- the cache-layout producer: scatter the prompts' K/V into their pages ----
     k_seq = [torch.randn(max_len, hk, d, device=dev, dtype=dt) for _ in range(b)]   # ground truth, contiguous
     v_seq = [torch.randn(max_len, hk, d, device=dev, dtype=dt) for _ in range(b)]
+    from vllm_flash_attn.cache_ops import reshape_and_cache_flash
+    slots = []
     for i, n in enumerate(prompt):
         pos = torch.arange(n, device=dev)
+        slots.append(bt[i, pos // page].long() * page + pos % page)
+    reshape_and_cache_flash(torch.cat([k_seq[i][:n] for i, n in enumerate(prompt)]), torch.cat([v_seq[i][:n] for i, n in enumerate(prompt)]),
+                            k_cache, v_cache, torch.cat(slots))
+    for i, n in enumerate(prompt):             # the writer against plain indexing
+        pos = torch.arange(n, device=dev)
         blk = bt[i, pos // page].long()
-        k_cache[blk, pos % page] = k_seq[i][:n]
-        v_cache[blk, pos % page] = v_seq[i][:n]
+        assert torch.equal(k_cache[blk, pos % page], k_seq[i][:n]) and torch.equal(v_cache[blk, pos % page], v_seq[i][:n])
 
     # ---- prefill: packed queries against the paged cache ----
     cu = torch.tensor([0] + list(torch.tensor(prompt).cumsum(0)), dtype=torch.int32)
@@ -96,3 +102,25 @@ def test_prefill_then_graph_captured_decode_loop():
         blk = bt[i, pos // page].long()
         assert torch.equal(k_cache[blk, pos % page], k_seq[i][n:n + steps])
         assert torch.equal(v_cache[blk, pos % page], v_seq[i][n:n + steps])
+
+
+def test_reshape_and_cache_flash_strided_inputs_and_padding_slots():
+    """The cache writer: K/V as strided views of one packed projection output (how a model hands them over), padding
+    tokens with slot -1 left out, every other cache row untouched."""
+    from vllm_flash_attn.cache_ops import reshape_and_cache_flash
+    torch.manual_seed(1)
+    dev, dt = "cuda", torch.float16
+    n, hk, d, page, nblk = 77, 4, 96, 32, 9
+    qkv = torch.randn(n, (8 + 2 * hk) * d, device=dev, dtype=dt)
+    key = qkv[:, 8 * d:(8 + hk) * d].view(n, hk, d)
+    value = qkv[:, (8 + hk) * d:].view(n, hk, d)
+    kc = torch.randn(nblk, page, hk, d, device=dev, dtype=dt); vc = torch.randn_like(kc)
+    kc0, vc0 = kc.clone(), vc.clone()
+    slot = torch.randperm(nblk * page, device=dev)[:n].to(torch.int64)
+    slot[5] = -1; slot[40] = -1
+    reshape_and_cache_flash(key, value, kc, vc, slot)
+    keep = slot >= 0
+    kc0.view(-1, hk, d)[slot[keep]] = key[keep]; vc0.view(-1, hk, d)[slot[keep]] = value[keep]
+    assert torch.equal(kc, kc0) and torch.equal(vc, vc0)
+    with pytest.raises(RuntimeError):
+        reshape_and_cache_flash(key, value, kc, vc, slot.to(torch.int32))

@@ -529,6 +529,31 @@ extern "C" int fa_b200_append_kv(FaFwdParams* a, void* stream) {
   return FA_OK;
 }
 
+// Cache writer for the caller's side of the path (vLLM: reshape_and_cache_flash): see fa_append.cu.
+extern "C" int fa_b200_reshape_and_cache(const void* key, const void* value, void* kcache, void* vcache, const int64_t* slot_mapping,
+                                         int num_tokens, int h_k, int d, int page_block_size, int64_t num_blocks,
+                                         int64_t key_token_stride, int64_t key_head_stride, int64_t value_token_stride, int64_t value_head_stride,
+                                         int64_t k_batch_stride, int64_t k_row_stride, int64_t k_head_stride,
+                                         int64_t v_batch_stride, int64_t v_row_stride, int64_t v_head_stride, void* stream) {
+  g_err[0] = 0;
+  FA_CHECK(num_tokens >= 0 && h_k > 0 && d > 0 && d % 8 == 0, "reshape_and_cache: bad shape (head dimension must be a multiple of 8)");
+  if (num_tokens == 0) return FA_OK;
+  FA_CHECK(key && value && kcache && vcache && slot_mapping, "reshape_and_cache: NULL pointer");
+  FA_CHECK(page_block_size > 0 && num_blocks > 0, "reshape_and_cache: bad page_block_size / num_blocks");
+  FA_CHECK((reinterpret_cast<uintptr_t>(key) | reinterpret_cast<uintptr_t>(value) | reinterpret_cast<uintptr_t>(kcache) | reinterpret_cast<uintptr_t>(vcache)) % 16 == 0 &&
+           (key_token_stride | key_head_stride | value_token_stride | value_head_stride | k_batch_stride | k_row_stride | k_head_stride |
+            v_batch_stride | v_row_stride | v_head_stride) % 8 == 0, "reshape_and_cache: tensors and strides must be 16-byte aligned");
+  CacheWriteParams a;
+  a.key = key; a.value = value; a.kcache = kcache; a.vcache = vcache; a.slot_mapping = slot_mapping;
+  a.key_token_stride = key_token_stride; a.key_head_stride = key_head_stride; a.value_token_stride = value_token_stride; a.value_head_stride = value_head_stride;
+  a.k_batch_stride = k_batch_stride; a.k_row_stride = k_row_stride; a.k_head_stride = k_head_stride;
+  a.v_batch_stride = v_batch_stride; a.v_row_stride = v_row_stride; a.v_head_stride = v_head_stride;
+  a.num_tokens = num_tokens; a.h_k = h_k; a.d = d; a.page = page_block_size;
+  cudaError_t e = launch_reshape_and_cache(a, (cudaStream_t)stream);
+  if (e != cudaSuccess) return fail(FA_ERR_CUDA, "CUDA error in cache-write kernel launch: %s", cudaGetErrorString(e));
+  return FA_OK;
+}
+
 // Will fa_b200_fwd_kvcache append p->knew / p->vnew (and apply rotary) inside its own kernel?  1 = yes (pass them to
 // fwd_kvcache directly: one launch), 0 = no (run fa_b200_append_kv first), negative = invalid arguments.
 extern "C" int fa_b200_fused_append_supported(const FaFwdParams* a) {

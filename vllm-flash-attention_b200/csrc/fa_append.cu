@@ -68,4 +68,34 @@ cudaError_t launch_append(const AppendParams& a, bool is_bf16, cudaStream_t stre
   return cudaGetLastError();
 }
 
+// ---- cache writer: token-major K/V rows -> their slots in the paged cache --------------------------------------------
+// What a serving engine runs once per step BEFORE attention (vLLM: reshape_and_cache_flash): token t's (h_k, d) row
+// goes to cache[slot / page][slot % page], slot = slot_mapping[t]; negative slots (padding tokens) are skipped.
+// One warp per (token, kv head), 16-byte chunks; element size 2 (fp16 / bf16).  Not part of the reference repository
+// ("the cache-layout / block_table producer", the component on the caller's side of the path).
+__global__ void __launch_bounds__(128) fa_reshape_and_cache_kernel(const CacheWriteParams a) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t item = (int64_t)blockIdx.x * 4 + warp;
+  if (item >= (int64_t)a.num_tokens * a.h_k) return;
+  const int t = (int)(item / a.h_k), hd = (int)(item - (int64_t)t * a.h_k);
+  const int64_t slot = a.slot_mapping[t];
+  if (slot < 0) return;
+  const int64_t blk = slot / a.page, in_page = slot - blk * a.page;
+  const uint16_t* ks = reinterpret_cast<const uint16_t*>(a.key) + (int64_t)t * a.key_token_stride + (int64_t)hd * a.key_head_stride;
+  const uint16_t* vs = reinterpret_cast<const uint16_t*>(a.value) + (int64_t)t * a.value_token_stride + (int64_t)hd * a.value_head_stride;
+  uint16_t* kd = reinterpret_cast<uint16_t*>(a.kcache) + blk * a.k_batch_stride + in_page * a.k_row_stride + (int64_t)hd * a.k_head_stride;
+  uint16_t* vd = reinterpret_cast<uint16_t*>(a.vcache) + blk * a.v_batch_stride + in_page * a.v_row_stride + (int64_t)hd * a.v_head_stride;
+  for (int c = lane; c < a.d / 8; c += 32) {
+    *reinterpret_cast<uint4*>(kd + c * 8) = *reinterpret_cast<const uint4*>(ks + c * 8);
+    *reinterpret_cast<uint4*>(vd + c * 8) = *reinterpret_cast<const uint4*>(vs + c * 8);
+  }
+}
+
+cudaError_t launch_reshape_and_cache(const CacheWriteParams& a, cudaStream_t stream) {
+  const int64_t items = (int64_t)a.num_tokens * a.h_k;
+  if (items == 0) return cudaSuccess;
+  fa_reshape_and_cache_kernel<<<(unsigned)((items + 3) / 4), 128, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+
 }  // namespace fa

@@ -60,6 +60,13 @@ struct AppendParams {
   int rot_by_qpos;                            // causal or local: q row i rotated at cache_len + i
 };
 cudaError_t launch_append(const AppendParams& a, bool is_bf16, cudaStream_t stream);
+struct CacheWriteParams {
+  const void* key; const void* value; void* kcache; void* vcache; const int64_t* slot_mapping;
+  int64_t key_token_stride, key_head_stride, value_token_stride, value_head_stride;
+  int64_t k_batch_stride, k_row_stride, k_head_stride, v_batch_stride, v_row_stride, v_head_stride;
+  int num_tokens, h_k, d, page;
+};
+cudaError_t launch_reshape_and_cache(const CacheWriteParams& a, cudaStream_t stream);
 
 // fa_prefill_tc5.cu — tcgen05/TMA/TMEM prefill kernel, every head dim 32..256 (multiples of 32).
 bool tc5_supported(const KParams& p);

@@ -56,6 +56,7 @@ EXPORTS = (
     "fa_b200_fwd", "fa_b200_varlen_fwd", "fa_b200_fwd_kvcache", "fa_b200_combine",
     "fa_b200_append_kv", "fa_b200_exchange_combine", "fa_b200_exchange_params_size",
     "fa_b200_fwd_kvcache_static_scratch", "fa_b200_fused_exchange_size", "fa_b200_fused_append_supported",
+    "fa_b200_reshape_and_cache",
 )
 STATIC_SCRATCH_BYTES = 4 << 20      # FA_B200_STATIC_SCRATCH_BYTES (include/fa_b200.h)
 
@@ -97,6 +98,8 @@ def _load():
         fn.argtypes = [C.POINTER(FaFwdParams), _vp]
     lib.fa_b200_fused_append_supported.restype = C.c_int
     lib.fa_b200_fused_append_supported.argtypes = [C.POINTER(FaFwdParams)]
+    lib.fa_b200_reshape_and_cache.restype = C.c_int
+    lib.fa_b200_reshape_and_cache.argtypes = [_vp] * 5 + [_i32] * 4 + [_i64] * 11 + [_vp]
     lib.fa_b200_combine.restype = C.c_int
     lib.fa_b200_combine.argtypes = [_vp, _vp, _vp, _vp, _i32, _i64, _i32, _i64, _i64, _i32, _i32, _vp]
     lib.fa_b200_exchange_combine.restype = C.c_int
