@@ -29,13 +29,16 @@ from ._cabi import FaFwdParams, OP_FWD, OP_KVCACHE, OP_VARLEN, check, lib
 _force_kernel = 0          # tests: _cabi.FA_KERNEL_* to pin a kernel family
 _two_step_append = False   # tests: always run the stand-alone append kernel (ctypes path only)
 
+host_binding_note = ""      # why the compiled binding is not in use, if it is not
 try:
     from . import _fa_torch as _N        # compiled host binding (optional; same library underneath)
     if _N.abi_version() != _cabi.ABI_VERSION:
-        raise ImportError(f"_fa_torch was built against ABI {_N.abi_version()}, libfa_b200.so has {_cabi.ABI_VERSION}: "
-                          "rebuild with build_torch_ext.sh")
-except ModuleNotFoundError:
+        host_binding_note = (f"_fa_torch was built against ABI {_N.abi_version()}, libfa_b200.so has {_cabi.ABI_VERSION}: "
+                             "rebuild with build_torch_ext.sh")
+        _N = None
+except (ImportError, OSError) as e:      # not built, or built against another torch: the ctypes binding serves
     _N = None
+    host_binding_note = f"{type(e).__name__}: {e}"
 _NATIVE = _N               # the loaded module, whatever _N is switched to later (tests toggle _N)
 if os.environ.get("FA_B200_HOST", "") == "ctypes":
     _N = None
