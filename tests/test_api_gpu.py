@@ -232,6 +232,39 @@ def test_fused_append_long_context_with_splits(sq, skn, causal, monkeypatch):
     assert torch.equal(q, q_keep) and torch.equal(kn, kn_keep)
 
 
+def test_fused_append_with_cache_batch_idx_and_alibi(monkeypatch):
+    """In-kernel append into a NON-paged cache addressed through cache_batch_idx (the rows must land in the indexed cache
+    entry), with ALiBi and interleaved partial rotary, fp16: bit-identical to the two-step path, other entries untouched."""
+    import vllm_flash_attn as fa
+    from vllm_flash_attn import vllm_flash_attn_2_cuda as ext
+    torch.manual_seed(9)
+    dev, dt = "cuda", torch.float16
+    b, bc, sq, skn, h, hk, d, sk = 3, 7, 1, 2, 8, 4, 64, 384
+    idx = torch.tensor([5, 0, 3], dtype=torch.int32, device=dev)
+    lens = torch.tensor([100, 382, 0], dtype=torch.int32, device=dev)       # middle, cache exactly filled, empty cache
+    kc0 = torch.randn(bc, sk, hk, d, device=dev, dtype=dt); vc0 = torch.randn_like(kc0)
+    q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
+    kn = torch.randn(b, skn, hk, d, device=dev, dtype=dt); vn = torch.randn_like(kn)
+    ang = torch.rand(sk, 16, device=dev) * 2 * math.pi                         # rotary_dim 32 of 64
+    cos, sin = torch.cos(ang).to(dt), torch.sin(ang).to(dt)
+    slopes = torch.rand(h, device=dev, dtype=torch.float32) * 0.2
+
+    def run(two_step):
+        monkeypatch.setattr(ext, "_two_step_append", two_step)
+        kc, vc = kc0.clone(), vc0.clone()
+        o, l = fa.flash_attn_with_kvcache(q, kc, vc, kn, vn, rotary_cos=cos, rotary_sin=sin, cache_seqlens=lens, cache_batch_idx=idx,
+                                          causal=True, rotary_interleaved=True, alibi_slopes=slopes, return_softmax_lse=True)
+        return o, l, kc, vc
+    of, lf, kf, vf = run(False)
+    ot, lt, kt, vt = run(True)
+    assert torch.equal(kf, kt) and torch.equal(vf, vt) and torch.equal(of, ot) and torch.equal(lf, lt)
+    untouched = [i for i in range(bc) if i not in (5, 0, 3)]
+    assert torch.equal(kf[untouched], kc0[untouched]) and torch.equal(vf[untouched], vc0[untouched])
+    for i, e in enumerate((5, 0, 3)):
+        L = int(lens[i])
+        assert torch.equal(vf[e, L:L + skn], vn[i]) and torch.equal(vf[e, :L], vc0[e, :L])
+
+
 def test_append_on_a_prefill_shape_takes_the_two_step_path():
     """64 new tokens per sequence against a cache (chunked prefill through flash_attn_with_kvcache): not a decode shape,
     so fa_b200_fused_append_supported says no and the bindings run the append kernel first; a sliding window does the
