@@ -4,7 +4,7 @@
 # Every ncu command is preceded by the same command without ncu (the recipe in B200_PROFILING.md).
 R=${1:-r02}
 O=gpurun_out
-SHORT="python bench.py --steps 2 --warmup 1 --no-sharded --no-ref-kernel --no-cpu"
+SHORT="python bench.py --steps 2 --warmup 1 --no-sharded --no-ref-kernel --no-cpu --no-sustained"
 python bench.py > $O/${R}_bench_line.json 2> $O/${R}_bench.err
 python bench.py --impl reference --steps 2 --warmup 1 > $O/${R}_bench_reference_arm.json 2>> $O/${R}_bench.err
 $SHORT > $O/plain1.log 2>&1 &&
