@@ -82,7 +82,7 @@ static bool as_single_page(const FaFwdParams* a, int op, KParams* k) {
 // caller stream).  Created on first use and kept for the life of the process (a handful of streams in practice).
 // The fork / join pattern is capture-safe: under stream capture the side stream joins the capture at the fork
 // event and leaves it at the join event.
-struct ForkSet { cudaStream_t side; cudaEvent_t fork, join; };
+struct ForkSet { cudaStream_t side, side2; cudaEvent_t fork, join, join2; };
 static ForkSet* get_fork_set(cudaStream_t main) {
   // per host thread: two threads that issue on the same stream must not share the fork / join events (an event records
   // the LAST cudaEventRecord: thread B's record between thread A's record and wait would let A's side stream start early)
@@ -93,9 +93,11 @@ static ForkSet* get_fork_set(cudaStream_t main) {
   auto it = sets.find(key);
   if (it != sets.end()) return &it->second;
   ForkSet f;
-  if (cudaStreamCreateWithFlags(&f.side, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+  if (cudaStreamCreateWithFlags(&f.side, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&f.side2, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
   if (cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) != cudaSuccess ||
-      cudaEventCreateWithFlags(&f.join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+      cudaEventCreateWithFlags(&f.join, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&f.join2, cudaEventDisableTiming) != cudaSuccess) return nullptr;
   return &sets.emplace(key, f).first->second;
 }
 
@@ -370,6 +372,7 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
       // without short sequences (a plain prefill) then pays nothing on its own stream for the decode launches that
       // find no work, and in a mixed batch the tails of the two halves overlap instead of running back to back.
       ForkSet* fs = nullptr;
+      bool forked2 = false;
       if (pl.decode_rows > 0) {
         // The decode kernel is instantiated for 16 and for 32 packed rows (the 32-row form holds twice the Q / O
         // fragments: fewer CTAs per SM and twice the MMA work per key).  Packed row counts are multiples of the
@@ -401,15 +404,23 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
           a->launches += 1;
         }
         if (e == cudaSuccess && second) {
+          // the 32-row form usually finds no sequence at all (it exists for 17..32 packed rows: a few-token chunk of a
+          // GQA model): on a side stream of its own, so that its launch and its empty CTAs run beside the 16-row
+          // launch instead of behind it
+          cudaStream_t ds2 = ds;
+          if (fs && g <= lo_rows && cudaStreamWaitEvent(fs->side2, fs->fork, 0) == cudaSuccess) { ds2 = fs->side2; forked2 = true; }
           kd.min_rows = lo_rows + 1; kd.max_rows = cap;
-          e = launch_decode(kd, pl.is_bf16, ds);
+          e = launch_decode(kd, pl.is_bf16, ds2);
           a->launches += 1;
+          if (forked2 && cudaEventRecord(fs->join2, fs->side2) != cudaSuccess) return fail(FA_ERR_CUDA, "mixed batch: event record failed");
         }
         if (fs && cudaEventRecord(fs->join, fs->side) != cudaSuccess) return fail(FA_ERR_CUDA, "mixed batch: event record failed");
+
         k.min_rows = cap + 1;
       }
       if (e == cudaSuccess) e = launch_prefill_tc5(k, pl.is_bf16, a->total_q, a->total_k, pl.num_sms, stream);
       if (fs && cudaStreamWaitEvent(stream, fs->join, 0) != cudaSuccess) return fail(FA_ERR_CUDA, "mixed batch: join failed");
+      if (forked2 && cudaStreamWaitEvent(stream, fs->join2, 0) != cudaSuccess) return fail(FA_ERR_CUDA, "mixed batch: join failed");
       break;
     }
     default: return fail(FA_ERR_INVALID, "unknown kernel id %d", pl.kernel);
