@@ -97,7 +97,10 @@ def test_workspace_matches_split_choice():
     P.num_splits = 0
     need = lib.fa_b200_workspace_bytes(C.byref(P), 2)
     s = lib.fa_b200_num_splits_heuristic(4, 296, 2, 128)
-    assert s == 2 and need == 16384 + s * 2 * 8 * 1 * (128 + 1) * 4 + 16     # counter head + partials + slack
+    if os.environ.get("FA_B200_STREAMK", "") not in ("", "0"):     # balanced ranges forced on: a pool of piece slots instead
+        assert need == 16384 + (2 * 148 + 4) * 16 * (128 + 1) * 4 + 16
+    else:
+        assert s == 2 and need == 16384 + s * 2 * 8 * 1 * (128 + 1) * 4 + 16     # counter head + partials + slack
     P.num_splits = 1
     assert lib.fa_b200_workspace_bytes(C.byref(P), 2) == 0
     P.num_splits = 129

@@ -99,7 +99,10 @@ def test_two_rank_shardings_match_single_gpu():
     assert "head_sharded" in ret and len(ret) == 13
     for name, (eo, el, ed) in ret.items():
         if name == "head_sharded":
-            assert eo == 0.0, (name, eo)                   # heads are independent: bit-identical
+            # heads are independent: the prefill rows are bit-identical; decode rows may differ by one bf16 rounding when
+            # the shard and the all-heads call cut their decode half into different pieces (split count / balanced ranges
+            # depend on the number of kv heads)
+            assert eo <= 4e-3, (name, eo)
         else:
             # two split trees (ranks x splits vs splits) of the same fp32 partials, output rounded to bf16 once
             assert eo <= 2e-2 and el <= 1e-3 and ed <= 2e-2, (name, eo, el, ed)

@@ -8,6 +8,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <climits>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <utility>
@@ -82,6 +83,22 @@ static bool as_single_page(const FaFwdParams* a, int op, KParams* k) {
 // caller stream).  Created on first use and kept for the life of the process (a handful of streams in practice).
 // The fork / join pattern is capture-safe: under stream capture the side stream joins the capture at the fork
 // event and leaves it at the join event.
+// Balanced-range decode (fa_decode_streamk_kernel).  Measured on B200 against the classic grid with the heuristic's split
+// count (profiles/r02_decode_streamk.txt): it wins where one CTA per (unit, equal piece) quantises badly against the 296
+// CTA slots or the lengths are ragged — the decode half of C4's TP shards: 192 sequences of 1024..4096 keys, 65.0 -> 58.5 us
+// at 1 KV head, 108 -> 98 us at 2 — and loses 5..10 us where the classic grid already fits (a CTA whose range crosses a
+// unit boundary pays the per-piece prologue and merge twice).  Default: the decode half of mixed batches with at least one
+// unit per SM; plain kvcache decode keeps the classic grid.  FA_B200_STREAMK=0 / 1 in the environment turns it off / on
+// wherever it is applicable (development, A/B measurements).
+static int streamk_mode() {
+  static const int mode = [] { const char* e = getenv("FA_B200_STREAMK"); return e ? (e[0] == '0' ? 0 : 1) : -1; }();
+  return mode;
+}
+static bool streamk_wanted(int64_t units, int num_sms, bool mixed_half) {
+  const int m = streamk_mode();
+  if (m >= 0) return m == 1;
+  return mixed_half && units >= num_sms;
+}
 struct ForkSet { cudaStream_t side, side2; cudaEvent_t fork, join, join2; };
 static ForkSet* get_fork_set(cudaStream_t main) {
   // per host thread: two threads that issue on the same stream must not share the fork / join events (an event records
@@ -112,6 +129,8 @@ struct Plan {
   bool fused_tail;   // decode kernel merges its own splits (and exchanges across GPUs): no separate combine launch
   size_t lse_floats, o_floats;   // split workspace payload: lse block (padded to 4 floats) | o block | [arrival counters]
   bool counters_in_head;
+  bool streamk;                // decode kernel in its balanced-range form (fa_decode_streamk_kernel)
+  int sk_slots;                // ... piece slots of its partial pool
   int mixed_splits;            // mixed varlen batch: split count of the decode half (>= 1)
   size_t mixed_part_off;       // ... byte offset of its partials in the workspace (behind the prefill work list)
   size_t mixed_lse_floats;
@@ -283,11 +302,27 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
     }
     FA_CHECK(splits <= 128, "num_splits > 128 not supported");                         // :217
   }
+  // Few units (small decode batches, TP shards with one or two KV heads): the decode kernel's balanced-range form — a
+  // fixed grid of 2 CTAs per SM, every CTA an equal share of ALL units' chunks (fa_decode.cu).  Taken whenever the
+  // split count is ours to choose; a caller's explicit num_splits keeps the classic grid.
+  pl->streamk = false; pl->sk_slots = 0;
+#ifndef FA_NO_STREAMK
+  if (kernel == FA_KERNEL_DECODE && may_split && a->seqlen_k > 0 && !(op == OP_KVCACHE && a->num_splits >= 1) &&
+      a->b <= 512 && (int64_t)a->b * a->h_k < 4 * (int64_t)num_sms * 2 && (size_t)a->b * a->h_k * sizeof(int) <= FA_B200_WS_HEAD_BYTES &&
+      streamk_wanted((int64_t)a->b * a->h_k, num_sms, false)) {
+    pl->streamk = true;
+    k.sk_grid = num_sms * 2; k.sk_min_per_cta = 8;
+    k.sk_rows = rows <= 16 ? 16 : 32;
+    pl->sk_slots = k.sk_grid + a->b * a->h_k;
+    const int max_chunks = (a->seqlen_k + 15) / 16;
+    splits = std::max(2, std::min(128, std::min(k.sk_grid, max_chunks)));     // reported as num_splits: pieces a unit can have at most
+  }
+#endif
   k.num_splits = pl->num_splits = splits;
   pl->num_sms = num_sms;
   // split workspace: lse block, padded to 4 floats so that the o block stays 16-byte aligned | o block | the arrival
   // counters of the decode kernel's in-kernel merge (when they are not part of a fused_exchange allocation)
-  const size_t part_rows = (size_t)splits * a->b * a->h * std::max(a->seqlen_q, 1);
+  const size_t part_rows = pl->streamk ? (size_t)pl->sk_slots * k.sk_rows : (size_t)splits * a->b * a->h * std::max(a->seqlen_q, 1);
   pl->lse_floats = (part_rows + 3) / 4 * 4;
   pl->o_floats = part_rows * a->d;
   pl->fused_tail = kernel == FA_KERNEL_DECODE && (splits > 1 || fx != nullptr);
@@ -304,8 +339,21 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
     // per unit leaves SMs idle and the longest context sets the time, so the half is split like a kvcache decode
     // (the reference consults the same heuristic for its GQA-packed varlen decode, flash_api.cpp:618-623).  Which
     // sequences are short is only known on the device: the count is taken as if all were.
+    pl->sk_slots = 0;
     if (pl->decode_rows > 0 && a->seqlen_k > 0 && (size_t)a->b * a->h_k * sizeof(int) <= FA_B200_WS_HEAD_BYTES) {
       const int ms = fa_b200_num_splits_heuristic(a->b * a->h_k, num_sms * 2, (a->seqlen_k + 255) / 256, 8);
+#ifndef FA_NO_STREAMK
+      if (a->b <= 512 && (int64_t)a->b * a->h_k < 4 * (int64_t)num_sms * 2 && streamk_wanted((int64_t)a->b * a->h_k, num_sms, true)) {
+        // few units: the balanced-range form of the decode kernel (see the kvcache case above); one pool of piece slots
+        // per launch of the half (16-row form, 32-row form)
+        pl->sk_slots = num_sms * 2 + a->b * a->h_k;
+        const size_t prow = (size_t)2 * pl->sk_slots * 32;
+        pl->mixed_splits = 2;
+        pl->mixed_lse_floats = (prow + 3) / 4 * 4;
+        pl->mixed_part_off = ((pl->ws_bytes ? pl->ws_bytes : (size_t)FA_B200_WS_HEAD_BYTES) + 15) / 16 * 16;
+        pl->ws_bytes = pl->mixed_part_off + (pl->mixed_lse_floats + prow * a->d) * sizeof(float);
+      } else
+#endif
       if (ms > 1) {
         const int pos = std::max(1, pl->decode_rows / k.group);                 // query positions a decode-half sequence can have
         const size_t prow = (size_t)ms * a->b * a->h * pos;
@@ -319,7 +367,17 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   return FA_OK;
 }
 
+static int run_plan_impl(FaFwdParams* a, int op, void* stream_);
+// num_splits is an in/out field (in: the caller's request, out: the count used).  A call that FAILS must leave the
+// request as it was: a caller that grows its workspace after FA_ERR_WORKSPACE and calls again with the same block would
+// otherwise turn the library's own choice of the first attempt into an explicit request of the second.
 static int run_plan(FaFwdParams* a, int op, void* stream_) {
+  const int requested = a ? a->num_splits : 0;
+  const int rc = run_plan_impl(a, op, stream_);
+  if (rc != FA_OK && a) a->num_splits = requested;
+  return rc;
+}
+static int run_plan_impl(FaFwdParams* a, int op, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   g_err[0] = 0;
   Plan pl;
@@ -395,6 +453,7 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
           kd.lse_accum = reinterpret_cast<float*>(reinterpret_cast<char*>(a->workspace) + pl.mixed_part_off);
           kd.o_accum = kd.lse_accum + pl.mixed_lse_floats;
           kd.split_counters = reinterpret_cast<int*>(a->workspace);
+          if (pl.sk_slots > 0) { kd.sk_grid = pl.num_sms * 2; kd.sk_min_per_cta = 8; kd.sk_rows = 32; }
           if (!a->workspace_clean && cudaMemsetAsync(kd.split_counters, 0, (size_t)a->b * a->h_k * sizeof(int), ds) != cudaSuccess)
             return fail(FA_ERR_CUDA, "mixed batch: clearing the split arrival counters failed");
         }
@@ -410,6 +469,10 @@ static int run_plan(FaFwdParams* a, int op, void* stream_) {
           cudaStream_t ds2 = ds;
           if (fs && g <= lo_rows && cudaStreamWaitEvent(fs->side2, fs->fork, 0) == cudaSuccess) { ds2 = fs->side2; forked2 = true; }
           kd.min_rows = lo_rows + 1; kd.max_rows = cap;
+          if (pl.sk_slots > 0) {            // its own pool of piece slots
+            kd.lse_accum += (size_t)pl.sk_slots * 32;
+            kd.o_accum += (size_t)pl.sk_slots * 32 * a->d;
+          }
           e = launch_decode(kd, pl.is_bf16, ds2);
           a->launches += 1;
           if (forked2 && cudaEventRecord(fs->join2, fs->side2) != cudaSuccess) return fail(FA_ERR_CUDA, "mixed batch: event record failed");

@@ -56,6 +56,10 @@ struct KParams {
   int64_t vnew_batch_stride, vnew_row_stride, vnew_head_stride;
   const void* rotary_cos; const void* rotary_sin;   // (seqlen_ro, rotary_dim / 2) or NULL
   int rotary_dim, seqlen_ro, rotary_interleaved, rot_by_qpos;
+  // ---- decode kernel: balanced ranges over all units (fa_decode_streamk_kernel) ----
+  int sk_grid;                                  // > 0: launch that kernel with this many CTAs
+  int sk_min_per_cta;                           // chunks per CTA at least
+  int sk_rows;                                  // rows per piece slot of the partial pool (sk_grid + b*h_k slots)
 };
 constexpr int FA_KP_MAX_PEERS = 8;
 

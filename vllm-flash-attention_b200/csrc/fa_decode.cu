@@ -36,12 +36,15 @@ struct DecodeCfg {
   static constexpr int SMEM = Q_BYTES + MAIN_BYTES + STAT_BYTES;
 };
 
+// One piece of one (sequence, kv head) unit: chunks [c_begin, c_end) of its KV range, as piece `split` of `nsp`.
+// cb_given < 0: the classic grid — piece `split` of p.num_splits equal pieces, range computed here; otherwise the range is
+// handed in (balanced-range kernel below).
 template <typename T, int D, int MT, int NW, int STAGES>
-__global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constant__ KParams p) {
+__device__ __forceinline__ void decode_unit(const KParams& p, uint8_t* smem, const int split, const int kvh, const int bidb,
+                                            const int nsp, const int cb_given, const int ce_given, const int slot0 = 0) {
   using Cfg = DecodeCfg<T, D, MT, NW, STAGES>;
   constexpr int ROWS = Cfg::ROWS;
   constexpr int CPR = D / 8;  // 16 B chunks per row
-  extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* q_sm = smem;
   uint8_t* ring = smem + Cfg::Q_BYTES;
   float* stat_m = reinterpret_cast<float*>(smem + Cfg::Q_BYTES + Cfg::MAIN_BYTES);
@@ -49,7 +52,6 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
   float* row_inv = stat_l + NW * ROWS;
   float* row_lse = row_inv + ROWS;
 
-  const int split = blockIdx.x, kvh = blockIdx.y, bidb = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = p.group;
   const SeqInfo si(p, bidb);
@@ -62,9 +64,9 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
   const int c_lo = max(w_first.lo, 0) / 16;
   const int c_hi = (max(w_last.hi, 0) + 15) / 16;
   const int n_chunks = max(c_hi - c_lo, 0);
-  const int per_split = (n_chunks + p.num_splits - 1) / p.num_splits;
-  const int c_begin = c_lo + split * per_split;
-  const int c_end = min(c_hi, c_begin + per_split);
+  const int per_split = (n_chunks + nsp - 1) / nsp;
+  const int c_begin = cb_given >= 0 ? cb_given : c_lo + split * per_split;
+  const int c_end = cb_given >= 0 ? min(ce_given, c_hi) : min(c_hi, c_begin + per_split);
 
   // ---- in-kernel append (flash_fwd_kernel.h:672-824): the call's new K/V rows, rotated, go into the cache here instead
   // of in a launch of their own.  Row L + i (L = length before the call) is written by the ONE CTA of this KV head whose
@@ -271,7 +273,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
         const bool empty = !(lt > 0.f);
         row_inv[row] = empty ? 0.f : 1.f / lt;
         // natural-log LSE = max*scale + ln(sum) (softmax.h:179); m is in log2 units
-        row_lse[row] = empty ? ((p.num_splits > 1 || p.partial || p.split_counters != nullptr || p.xchg_world > 0) ? -INFINITY : INFINITY)
+        row_lse[row] = empty ? ((nsp > 1 || p.partial || p.split_counters != nullptr || p.xchg_world > 0) ? -INFINITY : INFINITY)
                              : mt * 0.6931471805599453f + __logf(lt);
       }
     }
@@ -308,27 +310,34 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
     const int tid = threadIdx.x;
     const int unit = bidb * p.h_k + kvh;
     auto head_of = [&](int r, int& qpos) { qpos = r / g; return kvh * g + (r - qpos * g); };
-    if (p.num_splits > 1) {
+    // where piece s of this unit keeps row r of its partial: row index prow(r) + s * sstride of o_accum / lse_accum.
+    // Classic grid: the reference's (split, b, h, sq) layout.  Balanced ranges: a POOL of piece slots of p.sk_rows rows,
+    // the unit's pieces in consecutive slots from slot0 (= first CTA of the unit + unit index: unique, and at most
+    // gridDim.x + b*h_k slots exist however the ranges fall).
+    const bool pool = cb_given >= 0;
+    const int64_t sstride = pool ? (int64_t)p.sk_rows : (int64_t)p.b * p.h * p.part_seq_stride;
+    auto prow = [&](int r) -> int64_t {
+      if (pool) return (int64_t)slot0 * p.sk_rows + r;
+      int qpos; const int hd = head_of(r, qpos);
+      return ((int64_t)bidb * p.h + hd) * p.part_seq_stride + qpos;
+    };
+    if (nsp > 1) {
       // a. this split's partial, fp32 (split, b, h, sq[, d]) — the layout of the reference's accum buffers
       for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
         const int r = idx / (D / 4), c4 = idx % (D / 4);
-        int qpos; const int hd = head_of(r, qpos);
-        const int64_t orow = (((int64_t)split * p.b + bidb) * p.h + hd) * p.part_seq_stride + qpos;
+        const int64_t orow = prow(r) + split * sstride;
         const float inv = row_inv[r];
         float4 x = *reinterpret_cast<const float4*>(red + r * Cfg::RED_STRIDE + c4 * 4);
         x.x *= inv; x.y *= inv; x.z *= inv; x.w *= inv;
         *reinterpret_cast<float4*>(p.o_accum + orow * D + c4 * 4) = x;
       }
-      for (int r = tid; r < Rw; r += NW * 32) {
-        int qpos; const int hd = head_of(r, qpos);
-        p.lse_accum[(((int64_t)split * p.b + bidb) * p.h + hd) * p.part_seq_stride + qpos] = row_lse[r];
-      }
+      for (int r = tid; r < Rw; r += NW * 32) p.lse_accum[prow(r) + split * sstride] = row_lse[r];
       // b. arrival ticket: the last CTA of the unit carries on, the others are done
       __threadfence();
       __syncthreads();
       if (tid == 0) {
         const int t = atomicAdd(p.split_counters + unit, 1);
-        s_last = t == p.num_splits - 1;
+        s_last = t == nsp - 1;
         if (s_last) p.split_counters[unit] = 0;          // ready for the next launch
       }
       __syncthreads();
@@ -339,12 +348,10 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
       // splits with 16 independent 16-byte loads in flight — the partials sit in L2, and a walk with one or two loads in
       // flight per lane is what made this tail cost more than the streaming loop of a short split.  Fixed order:
       // deterministic.
-      const int S = p.num_splits;
-      const int64_t sstride = (int64_t)p.b * p.h * p.part_seq_stride;
+      const int S = nsp;
       float* wsm = red + ROWS * Cfg::RED_STRIDE;            // [Rw][S] weights, behind the O rows (the ring is free by now)
       for (int r = warp; r < Rw; r += NW) {
-        int qpos; const int hd = head_of(r, qpos);
-        const int64_t row0 = ((int64_t)bidb * p.h + hd) * p.part_seq_stride + qpos;
+        const int64_t row0 = prow(r);
         float ls[4], mx = -INFINITY;
 #pragma unroll
         for (int i = 0; i < 4; i++) {
@@ -372,8 +379,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
       __syncthreads();
       for (int idx = tid; idx < Rw * (D / 4); idx += NW * 32) {
         const int r = idx / (D / 4), c4 = idx % (D / 4);
-        int qpos; const int hd = head_of(r, qpos);
-        const float* src = p.o_accum + (((int64_t)bidb * p.h + hd) * p.part_seq_stride + qpos) * D + c4 * 4;
+        const float* src = p.o_accum + prow(r) * D + c4 * 4;
         const float* wr = wsm + r * S;
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         int s2 = 0;
@@ -524,7 +530,7 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
     }
     return;
   }
-  if ((p.num_splits > 1 || p.partial)) {
+  if ((nsp > 1 || p.partial)) {
     // fp32 partials, (split, b, h, sq[, d]) like the reference's accum buffers (flash_api.cpp:212-213)
     for (int idx = threadIdx.x; idx < Rw * (D / 4); idx += NW * 32) {
       int r = idx / (D / 4), c4 = idx % (D / 4);
@@ -563,8 +569,98 @@ __global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constan
 }
 
 template <typename T, int D, int MT, int NW, int STAGES>
+__global__ void __launch_bounds__(NW * 32) fa_decode_kernel(const __grid_constant__ KParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  decode_unit<T, D, MT, NW, STAGES>(p, smem, blockIdx.x, blockIdx.y, blockIdx.z, p.num_splits, -1, -1);
+}
+
+// Balanced ranges ("stream-K" over the KV axis) for launches with FEW units (b * h_k below a few waves of CTAs) — small
+// decode batches, TP shards with one or two KV heads, the decode half of a mixed batch.  One CTA per (unit, equal piece)
+// then suffers twice: pieces of ragged sequences differ in size, and piece counts quantise badly against the SM count
+// (192 units x 3 pieces = 1.95 waves of unequal CTAs: 3.8 TB/s where the same bytes in equal shares stream at 4.6).  Here
+// the grid is a fixed 2 CTAs per SM and the chunks of ALL units, laid end to end, are cut into gridDim.x equal ranges:
+// CTA c owns chunks [c * per, (c + 1) * per) of that line, i.e. the tail of one unit, maybe whole units, the head of
+// another — each such segment is one call of decode_unit with its piece index and the unit's piece count, and the unit's
+// last arriver merges the pieces as before (same fused tail, same arrival counters, same cross-GPU exchange).  Every CTA
+// derives the same layout from the sequence lengths itself (one pass over the batch, a prefix sum in shared memory):
+// no scheduling kernel in front.  `per` is at least p.sk_min_per_cta, which bounds the pieces of a unit and so the
+// partial buffers (host: fa_api.cu).
+constexpr int SK_MAX_B = 512;
+template <typename T, int D, int MT, int NW, int STAGES>
+__global__ void __launch_bounds__(NW * 32) fa_decode_streamk_kernel(const __grid_constant__ KParams p) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int s_w[SK_MAX_B], s_clo[SK_MAX_B], s_pref[SK_MAX_B + 1];
+  __shared__ int s_wmax, s_units;
+  const int tid = threadIdx.x;
+  for (int b = tid; b < p.b; b += NW * 32) {
+    const SeqInfo si(p, b);
+    const int R = si.sq * p.group;
+    int w = 0, clo = 0;
+    if (si.sq > 0 && R >= p.min_rows && R <= p.max_rows) {            // served by this launch (mixed batches: decode sequences only)
+      const RowWindow wf = row_window(p, 0, si.sq, si.sk), wl = row_window(p, si.sq - 1, si.sq, si.sk);
+      clo = max(wf.lo, 0) / 16;
+      w = max(max((max(wl.hi, 0) + 15) / 16 - clo, 0), 1);            // a sequence without visible keys still has its rows written
+    }
+    s_w[b] = w; s_clo[b] = clo;
+  }
+  __syncthreads();
+  if (tid < 32) {                                                      // exclusive prefix sum over <= 512 sequences: one warp, 16 per lane
+    int loc[SK_MAX_B / 32], sum = 0;
+#pragma unroll
+    for (int i = 0; i < SK_MAX_B / 32; i++) { const int b = tid * (SK_MAX_B / 32) + i; loc[i] = sum; sum += b < p.b ? s_w[b] : 0; }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, incl, o); if (tid >= o) incl += y; }
+    const int base = incl - sum;
+#pragma unroll
+    for (int i = 0; i < SK_MAX_B / 32; i++) { const int b = tid * (SK_MAX_B / 32) + i; if (b < p.b) s_pref[b] = base + loc[i]; }
+    int wmax = 0;
+#pragma unroll
+    for (int i = 0; i < SK_MAX_B / 32; i++) { const int b = tid * (SK_MAX_B / 32) + i; if (b < p.b) wmax = max(wmax, s_w[b]); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+    int served = 0;
+#pragma unroll
+    for (int i = 0; i < SK_MAX_B / 32; i++) { const int b = tid * (SK_MAX_B / 32) + i; if (b < p.b && s_w[b] > 0) served++; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) served += __shfl_xor_sync(0xffffffffu, served, o);
+    if (tid == 31) { s_pref[p.b] = incl; s_wmax = wmax; s_units = served; }
+  }
+  __syncthreads();
+  const long long total = (long long)s_pref[p.b] * p.h_k;
+  // chunks per CTA: an equal share; at least p.sk_min_per_cta (a warp should see a few chunks); and enough that no unit
+  // is cut into more pieces than the merge takes (128)
+  // (the floor must not pile whole units onto one CTA while others idle: at least one CTA per served unit)
+  const long long n_act = min((long long)gridDim.x, max((long long)s_units * p.h_k, (total + p.sk_min_per_cta - 1) / p.sk_min_per_cta));
+  const int per = max((int)((total + n_act - 1) / max(n_act, 1ll)), (s_wmax + 126) / 127);
+  long long g = (long long)blockIdx.x * per;
+  const long long g_end = min(total, g + per);
+  while (g < g_end) {
+    // sequence that holds global chunk g: largest b with h_k * pref[b] <= g (sequences with weight 0 are skipped by the search)
+    int lo = 0, hi = p.b;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if ((long long)s_pref[mid] * p.h_k <= g) lo = mid; else hi = mid; }
+    const int b = lo, w = s_w[b];
+    const long long in_seq = g - (long long)s_pref[b] * p.h_k;
+    const int kvh = (int)(in_seq / w), local = (int)(in_seq - (long long)kvh * w);
+    const int seg = (int)min((long long)(w - local), g_end - g);
+    const long long unit0 = g - local;                                 // first global chunk of this unit
+    const int first_cta = (int)(unit0 / per), last_cta = (int)((unit0 + w - 1) / per);
+    decode_unit<T, D, MT, NW, STAGES>(p, smem, (int)blockIdx.x - first_cta, kvh, b, last_cta - first_cta + 1,
+                                      s_clo[b] + local, s_clo[b] + local + seg, first_cta + b * p.h_k + kvh);
+    g += seg;
+    __syncthreads();                                                   // shared memory is reused by the next segment
+  }
+}
+
+template <typename T, int D, int MT, int NW, int STAGES>
 static cudaError_t launch_decode_t(const KParams& p, cudaStream_t stream) {
   using Cfg = DecodeCfg<T, D, MT, NW, STAGES>;
+  if (p.sk_grid > 0) {
+    auto kern = fa_decode_streamk_kernel<T, D, MT, NW, STAGES>;
+    FA_SET_SMEM_ONCE(kern, Cfg::SMEM);
+    kern<<<p.sk_grid, NW * 32, Cfg::SMEM, stream>>>(p);
+    return cudaGetLastError();
+  }
   auto kern = fa_decode_kernel<T, D, MT, NW, STAGES>;
   FA_SET_SMEM_ONCE(kern, Cfg::SMEM);
   dim3 grid(p.num_splits, p.h_k, p.b);
