@@ -1,9 +1,8 @@
 """GPU: the decode kernel's balanced-range form (fa_decode_streamk_kernel: a fixed grid of 2 CTAs per SM, every CTA an equal
-share of ALL units' KV chunks, pieces of a unit merged by its last arriver).  By default it serves the decode half of
-mixed batches with at least one (sequence, kv head) unit per SM — checked here in-process on a TP-shard-like batch — and
-FA_B200_STREAMK=1 switches it on wherever it is applicable; the decode / kvcache / append / fuzz tests are then re-run
-in a subprocess with that setting, so that every mask, page size, head dim, split merge and the in-kernel append are
-checked on it as well."""
+share of ALL units' KV chunks, pieces of a unit merged by its last arriver).  It is opt-in (FA_B200_STREAMK=1; measured
+wins and losses: profiles/r02_decode_streamk.txt), so the decode / kvcache / append / fuzz tests and a TP-shard-like
+mixed batch are re-run in a subprocess with that setting: every mask, page size, head dim, split merge and the in-kernel
+append are checked on it as well.  The mixed batch is also checked in-process on the default (classic) grid."""
 import os
 import subprocess
 import sys
@@ -41,7 +40,7 @@ def test_mixed_batch_decode_half_on_balanced_ranges():
     reshape_and_cache_flash(k, v, kc, vc, slots)
     out = fa.flash_attn_varlen_func(q, kc, vc, cu_q.to(dev), cu_k.to(dev), max(lens_q), max(lens_k), causal=True, block_table=bt)
     info = dict(ext.last_call_info)
-    assert info["kernel_used"] == 1 and info["num_splits"] == 2, info          # 2: the decode half runs on balanced ranges
+    assert info["kernel_used"] == 1 and info["num_splits"] > 1, info           # the decode half is split (classic grid unless forced)
     ref32, _ = orc.attention_ref_varlen(q, k, v, cu_q, cu_k, causal=True)
     pt, _ = orc.attention_ref_varlen(q, k, v, cu_q, cu_k, causal=True, upcast=False, reorder_ops=True)
     err, err_pt = (out.float() - ref32.float()).abs().max().item(), (pt.float() - ref32.float()).abs().max().item()
@@ -58,7 +57,7 @@ def test_decode_tests_again_with_balanced_ranges_forced_on():
            os.path.join(ROOT, "tests", "test_parity_gpu.py"), os.path.join(ROOT, "tests", "test_fuzz_gpu.py"),
            os.path.join(ROOT, "tests", "test_api_gpu.py"), os.path.join(ROOT, "tests", "test_serving_loop_gpu.py"),
            os.path.join(ROOT, "tests", "test_zz_no_alloc.py"), os.path.join(ROOT, "tests", "test_torch_ext.py"),
-           os.path.join(ROOT, "tests", "test_cabi.py"),
-           "-k", "not four_threads"]
+           os.path.join(ROOT, "tests", "test_cabi.py"), os.path.join(ROOT, "tests", "test_streamk_gpu.py"),
+           "-k", "not four_threads and not forced_on"]
     r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=1200, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]

@@ -87,17 +87,19 @@ static bool as_single_page(const FaFwdParams* a, int op, KParams* k) {
 // count (profiles/r02_decode_streamk.txt): it wins where one CTA per (unit, equal piece) quantises badly against the 296
 // CTA slots or the lengths are ragged — the decode half of C4's TP shards: 192 sequences of 1024..4096 keys, 65.0 -> 58.5 us
 // at 1 KV head, 108 -> 98 us at 2 — and loses 5..10 us where the classic grid already fits (a CTA whose range crosses a
-// unit boundary pays the per-piece prologue and merge twice).  Default: the decode half of mixed batches with at least one
-// unit per SM; plain kvcache decode keeps the classic grid.  FA_B200_STREAMK=0 / 1 in the environment turns it off / on
-// wherever it is applicable (development, A/B measurements).
+// unit boundary pays the per-piece prologue and merge twice).  Inside the whole mixed call the gain does not survive
+// either: C4's TP=8 shard 0.1269 -> 0.1233 ms eager but 0.1178 -> 0.1272 ms under a CUDA graph — the classic grid's many
+// small CTAs drain unevenly and the prefill CTAs (which cannot share an SM with a decode CTA) start in the gaps, the
+// balanced grid ends all at once.  So the form is OPT-IN: FA_B200_STREAMK=1 in the environment turns it on wherever it
+// is applicable (ragged decode batches, very large totals, development); default off.
 static int streamk_mode() {
   static const int mode = [] { const char* e = getenv("FA_B200_STREAMK"); return e ? (e[0] == '0' ? 0 : 1) : -1; }();
   return mode;
 }
 static bool streamk_wanted(int64_t units, int num_sms, bool mixed_half) {
   const int m = streamk_mode();
-  if (m >= 0) return m == 1;
-  return mixed_half && units >= num_sms;
+  (void)units; (void)num_sms; (void)mixed_half;
+  return m == 1;
 }
 struct ForkSet { cudaStream_t side, side2; cudaEvent_t fork, join, join2; };
 static ForkSet* get_fork_set(cudaStream_t main) {
