@@ -51,6 +51,31 @@ extern "C" int fa_b200_num_splits_heuristic(int work, int num_sms, int num_n_blo
   return 1;
 }
 
+// Decode kernel: the rule above with two corrections measured on B200 (profiles/r02_decode_split_sweep.jsonl: explicit
+// split counts against the automatic one, 20-256 sequences x 8 kv heads; slots = 2 resident CTAs per SM, blocks of 256
+// keys).  (1) 1.0-1.5 waves of units (the reference never splits above 0.8 waves): the second wave runs almost empty, so
+// 2-4 pieces per unit are taken when they fill the waves better AND a piece keeps >= 1024 keys (48 sequences: 4096 keys
+// 168 -> 149 us, 16384 keys 630 -> 516 us).  (2) Pieces shorter than 1024 keys must not spill into a second wave — a
+// piece's fixed cost (prologue chain, partial write, ticket, merge) is then as long as its stream (24 sequences x 1024
+// keys: 4 splits 38.5 us, 1 split 26.7 us; 20 sequences x 4096 keys: 8 splits -> 3, 73.9 us).
+static int decode_splits(int work, int slots, int n_blocks) {
+  constexpr int kMinBlocks = 4;
+  auto eff = [&](int s) { const float w = float(work) * s / slots; return w / std::ceil(w); };
+  int s = fa_b200_num_splits_heuristic(work, slots, n_blocks, 128);
+  if (s == 1 && work > slots && eff(1) < 0.75f) {
+    float best = eff(1);
+    for (int t = 2; t <= 4; t++) if (n_blocks / t >= kMinBlocks) best = std::max(best, eff(t));
+    for (int t = 1; t <= 4; t++) if ((t == 1 || n_blocks / t >= kMinBlocks) && eff(t) >= 0.85f * best) { s = t; break; }
+  }
+  auto fits = [&](int t) { return t == 1 || n_blocks / t >= kMinBlocks || (int64_t)work * t <= slots; };
+  if (!fits(s)) {                              // the best-filling count below it that keeps its pieces long or in one wave
+    int bs = 1; float be = eff(1);
+    for (int t = 2; t < s; t++) if (fits(t) && eff(t) > be + 1e-3f) { be = eff(t); bs = t; }
+    s = bs;
+  }
+  return s;
+}
+
 static int device_sms() {
   static int sms[64] = {0};
   int dev = 0;
@@ -300,7 +325,8 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
       const int n_blocks = (a->seqlen_k + blk - 1) / blk;
       const int work = kernel == FA_KERNEL_DECODE ? a->b * a->h_k
                                                   : a->b * a->h * ((a->seqlen_q + 63) / 64);
-      splits = fa_b200_num_splits_heuristic(work, num_sms * 2, n_blocks, 128);
+      splits = kernel == FA_KERNEL_DECODE ? decode_splits(work, num_sms * 2, n_blocks)
+                                          : fa_b200_num_splits_heuristic(work, num_sms * 2, n_blocks, 128);
     }
     FA_CHECK(splits <= 128, "num_splits > 128 not supported");                         // :217
   }
