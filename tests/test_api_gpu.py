@@ -572,6 +572,40 @@ def test_split_decode_merges_in_kernel():
     assert (out.float() - ref32.float()).abs().max().item() <= 3 * (pt.float() - ref32.float()).abs().max().item() + 1e-5
 
 
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("paged,sq,splits,window,alibi", [
+    (True, 1, 1, (-1, -1), False), (True, 1, 3, (-1, -1), True), (False, 3, 3, (-1, -1), False),
+    (True, 3, 2, (3000, 0), False), (False, 1, 4, (-1, -1), True), (True, 4, 1, (-1, -1), False)])
+def test_decode_one_wave_of_long_pieces_takes_the_12_warp_form(paged, sq, splits, window, alibi, dt):
+    """d = 128, at most 16 packed rows, every piece resident at once and >= 2048 keys long: fa_api.cu sets wide_cta and
+    the decode kernel runs 6 warps x 2 stages per CTA (profiles/r02_decode_wide_cta.txt).  Same contract as every kvcache
+    call: ragged lengths (one of 16 keys: empty pieces), masks, ALiBi, both cache layouts, in-kernel split merge."""
+    import vllm_flash_attn as fa
+    torch.manual_seed(11)
+    dev, b, h, hk, d, page, smax = "cuda", 3, 32, 8, 128, 16, 9008
+    lens = torch.tensor([9000, 4097, 16], dtype=torch.int32, device=dev)
+    q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
+    k = torch.randn(b, smax, hk, d, device=dev, dtype=dt); v = torch.randn_like(k)
+    slopes = (torch.rand(b, h, device=dev) * 0.3) if alibi else None
+    if paged:
+        nblk = b * smax // page
+        bt = torch.randperm(nblk, device=dev).to(torch.int32).view(b, -1).contiguous()
+        kc = torch.empty(nblk, page, hk, d, device=dev, dtype=dt); vc = torch.empty_like(kc)
+        kc[bt.long().flatten()] = k.view(b * smax // page, page, hk, d); vc[bt.long().flatten()] = v.view(b * smax // page, page, hk, d)
+        out, lse = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=lens, block_table=bt, causal=True, window_size=window,
+                                              alibi_slopes=slopes, num_splits=splits, return_softmax_lse=True)
+    else:
+        out, lse = fa.flash_attn_with_kvcache(q, k, v, cache_seqlens=lens, causal=True, window_size=window,
+                                              alibi_slopes=slopes, num_splits=splits, return_softmax_lse=True)
+    kmask = torch.arange(smax, device=dev).expand(b, smax) < lens.view(-1, 1)
+    bias = orc.attn_bias_from_alibi_slopes(slopes, sq, smax, None, kmask, causal=True) if alibi else None
+    ref32, _ = orc.attention_ref(q, k, v, None, kmask, bias, causal=True, window_size=window)
+    pt, _ = orc.attention_ref(q, k, v, None, kmask, bias, causal=True, window_size=window, upcast=False, reorder_ops=True)
+    err, err_pt = (out.float() - ref32.float()).abs().max().item(), (pt.float() - ref32.float()).abs().max().item()
+    assert not torch.isnan(out.float()).any() and torch.isfinite(lse).all()
+    assert err <= 3 * err_pt + 1e-5, (err, err_pt)
+
+
 def test_varlen_seqused_k():
     """varlen_fwd(seqused_k=...) (flash_api.cpp:428,:553-556; BlockInfo src/block_info.h:24): keys beyond
     seqused_k[b] are ignored although cu_seqlens_k spans them.  Prefill rows run on the tcgen05 kernel,

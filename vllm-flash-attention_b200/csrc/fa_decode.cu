@@ -705,6 +705,11 @@ static cudaError_t launch_decode_d(const KParams& p, int mt, cudaStream_t stream
     if (mt == 1) return launch_decode_t<T, D_, 1, NW_, ST_>(p, stream);              \
     if constexpr (D_ <= 128) { if (mt == 2) return launch_decode_t<T, D_, 2, NW_, ST_>(p, stream); } \
     break;
+  // d = 128, all pieces resident at once and long (fa_api.cu sets wide_cta): 12 warps per SM keep more loads in flight than
+  // 8 — 6 warps x 2 stages, same ring bytes.  C5 on one GPU: B=8 0.623 -> 0.589 ms, B=1 0.0939 -> 0.0916 ms; contexts of
+  // 16k+ 2-4 % (profiles/r02_decode_wide_cta.txt).  Batches of several waves (C3) stay at 4 x 3: 6.83 against 6.74 TB/s.
+  // Up to 16 packed rows only: the 32-row form needs 245 registers per thread, and 192 such threads leave one CTA per SM.
+  if (p.d == 128 && p.wide_cta && p.sk_grid == 0 && mt == 1) return launch_decode_t<T, 128, 1, 6, 2>(p, stream);
   switch (p.d) {
     FA_DEC_CASE(32, FA_DEC32_NW, FA_DEC32_ST)
     FA_DEC_CASE(64, FA_DEC64_NW, FA_DEC64_ST)
