@@ -606,6 +606,40 @@ def test_decode_one_wave_of_long_pieces_takes_the_12_warp_form(paged, sq, splits
     assert err <= 3 * err_pt + 1e-5, (err, err_pt)
 
 
+@pytest.mark.parametrize("paged,alibi,sq", [(True, False, 1), (True, True, 2), (False, False, 1)])
+def test_decode_many_waves_takes_the_three_cta_per_sm_form(paged, alibi, sq):
+    """d = 128, >= 10 units per SM, one split: 4 warps x 2 stages, three CTAs per SM (fa_api.cu wide_cta = 2;
+    profiles/r02_decode_wide_cta.txt).  1536 units of ragged short contexts (some empty, some of one key)."""
+    import vllm_flash_attn as fa
+    torch.manual_seed(12)
+    dev, dt, b, h, hk, d, page, smax = "cuda", torch.bfloat16, 192, 16, 8, 128, 16, 320
+    lens = torch.randint(0, smax + 1, (b,), device=dev).to(torch.int32)
+    lens[0], lens[1], lens[2] = 0, 1, smax
+    if sq > 1: lens = lens.clamp(min=sq)          # a causal row needs its own key
+    q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
+    k = torch.randn(b, smax, hk, d, device=dev, dtype=dt); v = torch.randn_like(k)
+    slopes = (torch.rand(b, h, device=dev) * 0.3) if alibi else None
+    if paged:
+        nblk = b * smax // page
+        bt = torch.randperm(nblk, device=dev).to(torch.int32).view(b, -1).contiguous()
+        kc = torch.empty(nblk, page, hk, d, device=dev, dtype=dt); vc = torch.empty_like(kc)
+        kc[bt.long().flatten()] = k.view(nblk, page, hk, d); vc[bt.long().flatten()] = v.view(nblk, page, hk, d)
+        out = fa.flash_attn_with_kvcache(q, kc, vc, cache_seqlens=lens, block_table=bt, causal=True, alibi_slopes=slopes)
+    else:
+        out = fa.flash_attn_with_kvcache(q, k, v, cache_seqlens=lens, causal=True, alibi_slopes=slopes)
+    info = dict(_ext().last_call_info)
+    assert info["kernel_used"] == 3 and info["num_splits"] == 1, info
+    kmask = torch.arange(smax, device=dev).expand(b, smax) < lens.view(-1, 1)
+    bias = orc.attn_bias_from_alibi_slopes(slopes, sq, smax, None, kmask, causal=True) if alibi else None
+    ref32, _ = orc.attention_ref(q, k, v, None, kmask, bias, causal=True)
+    pt, _ = orc.attention_ref(q, k, v, None, kmask, bias, causal=True, upcast=False, reorder_ops=True)
+    live = (lens > 0).view(-1, 1, 1, 1)            # a sequence without keys: the reference leaves zeros, the oracle NaN
+    err = ((out.float() - ref32.float()) * live).nan_to_num(0).abs().max().item()
+    err_pt = ((pt.float() - ref32.float()) * live).nan_to_num(0).abs().max().item()
+    assert not torch.isnan(out.float()).any() and (sq > 1 or (out[0] == 0).all())
+    assert err <= 3 * err_pt + 1e-5, (err, err_pt)
+
+
 def test_varlen_seqused_k():
     """varlen_fwd(seqused_k=...) (flash_api.cpp:428,:553-556; BlockInfo src/block_info.h:24): keys beyond
     seqused_k[b] are ignored although cu_seqlens_k spans them.  Prefill rows run on the tcgen05 kernel,

@@ -351,6 +351,8 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   // one wave of long pieces: the 12-warp form of the d = 128 decode kernel (fa_decode.cu launch_decode_d)
   k.wide_cta = kernel == FA_KERNEL_DECODE && a->d == 128 && rows <= 16 && !pl->streamk && splits >= 1 &&
                (int64_t)a->b * a->h_k * splits <= 2 * (int64_t)num_sms && a->seqlen_k / splits >= 2048;
+  if (kernel == FA_KERNEL_DECODE && a->d == 128 && rows <= 16 && !pl->streamk && splits == 1 && !fx &&
+      (int64_t)a->b * a->h_k >= 10 * (int64_t)num_sms) k.wide_cta = 2;      // >= 5 waves of 2 CTAs per SM: three smaller CTAs per SM
   // split workspace: lse block, padded to 4 floats so that the o block stays 16-byte aligned | o block | the arrival
   // counters of the decode kernel's in-kernel merge (when they are not part of a fused_exchange allocation)
   const size_t part_rows = pl->streamk ? (size_t)pl->sk_slots * k.sk_rows : (size_t)splits * a->b * a->h * std::max(a->seqlen_q, 1);

@@ -60,7 +60,7 @@ struct KParams {
   int sk_grid;                                  // > 0: launch that kernel with this many CTAs
   int sk_min_per_cta;                           // chunks per CTA at least
   int sk_rows;                                  // rows per piece slot of the partial pool (sk_grid + b*h_k slots)
-  int wide_cta;                                 // decode, d = 128: 6 warps x 2 stages per CTA instead of 4 x 3 (one wave of long pieces)
+  int wide_cta;                                 // decode, d = 128, instead of 4 warps x 3 stages: 1 = 6 x 2 (one wave of long pieces), 2 = 4 x 2, three CTAs per SM (many waves)
 };
 constexpr int FA_KP_MAX_PEERS = 8;
 

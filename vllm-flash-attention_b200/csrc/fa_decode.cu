@@ -709,7 +709,11 @@ static cudaError_t launch_decode_d(const KParams& p, int mt, cudaStream_t stream
   // 8 — 6 warps x 2 stages, same ring bytes.  C5 on one GPU: B=8 0.623 -> 0.589 ms, B=1 0.0939 -> 0.0916 ms; contexts of
   // 16k+ 2-4 % (profiles/r02_decode_wide_cta.txt).  Batches of several waves (C3) stay at 4 x 3: 6.83 against 6.74 TB/s.
   // Up to 16 packed rows only: the 32-row form needs 245 registers per thread, and 192 such threads leave one CTA per SM.
-  if (p.d == 128 && p.wide_cta && p.sk_grid == 0 && mt == 1) return launch_decode_t<T, 128, 1, 6, 2>(p, stream);
+  if (p.d == 128 && p.wide_cta == 1 && p.sk_grid == 0 && mt == 1) return launch_decode_t<T, 128, 1, 6, 2>(p, stream);
+  // Five waves and more (wide_cta == 2): 4 warps x 2 stages, a 64 KB ring, THREE CTAs per SM — a launch's fixed cost is paid
+  // per wave of resident CTAs (zero-length contexts, 2048 units: 32.8 -> 24.6 us) and 12 warps per SM hold up better in
+  // the sustained regime (2048 units x 4096 keys, 200 replays: 680 -> 654 us; the bench's 20-call C3 is the same either way).
+  if (p.d == 128 && p.wide_cta == 2 && p.sk_grid == 0 && mt == 1) return launch_decode_t<T, 128, 1, 4, 2>(p, stream);
   switch (p.d) {
     FA_DEC_CASE(32, FA_DEC32_NW, FA_DEC32_ST)
     FA_DEC_CASE(64, FA_DEC64_NW, FA_DEC64_ST)
