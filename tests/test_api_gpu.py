@@ -577,13 +577,13 @@ def test_split_decode_merges_in_kernel():
     (True, 1, 1, (-1, -1), False), (True, 1, 3, (-1, -1), True), (False, 3, 3, (-1, -1), False),
     (True, 3, 2, (3000, 0), False), (False, 1, 4, (-1, -1), True), (True, 4, 1, (-1, -1), False)])
 def test_decode_one_wave_of_long_pieces_takes_the_12_warp_form(paged, sq, splits, window, alibi, dt):
-    """d = 128, at most 16 packed rows, every piece resident at once and >= 2048 keys long: fa_api.cu sets wide_cta and
+    """d = 128, at most 16 packed rows, every piece resident at once and >= 4096 keys long: fa_api.cu sets wide_cta and
     the decode kernel runs 6 warps x 2 stages per CTA (profiles/r02_decode_wide_cta.txt).  Same contract as every kvcache
     call: ragged lengths (one of 16 keys: empty pieces), masks, ALiBi, both cache layouts, in-kernel split merge."""
     import vllm_flash_attn as fa
     torch.manual_seed(11)
-    dev, b, h, hk, d, page, smax = "cuda", 3, 32, 8, 128, 16, 9008
-    lens = torch.tensor([9000, 4097, 16], dtype=torch.int32, device=dev)
+    dev, b, h, hk, d, page, smax = "cuda", 3, 32, 8, 128, 16, 17008
+    lens = torch.tensor([17000, 4097, 16], dtype=torch.int32, device=dev)
     q = torch.randn(b, sq, h, d, device=dev, dtype=dt)
     k = torch.randn(b, smax, hk, d, device=dev, dtype=dt); v = torch.randn_like(k)
     slopes = (torch.rand(b, h, device=dev) * 0.3) if alibi else None

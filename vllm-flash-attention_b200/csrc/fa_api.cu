@@ -348,9 +348,11 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
 #endif
   k.num_splits = pl->num_splits = splits;
   pl->num_sms = num_sms;
-  // one wave of long pieces: the 12-warp form of the d = 128 decode kernel (fa_decode.cu launch_decode_d)
+  // one wave of long pieces: the 12-warp form of the d = 128 decode kernel (fa_decode.cu launch_decode_d).  seqlen_k is the
+  // cache's capacity (block-table width), not the lengths on the device: a wide table over short contexts picks it too
+  // and pays its larger fixed cost (8 sequences x 1024 keys: 16.4 -> 18.2 us), hence the high bar of 4096 keys per piece.
   k.wide_cta = kernel == FA_KERNEL_DECODE && a->d == 128 && rows <= 16 && !pl->streamk && splits >= 1 &&
-               (int64_t)a->b * a->h_k * splits <= 2 * (int64_t)num_sms && a->seqlen_k / splits >= 2048;
+               (int64_t)a->b * a->h_k * splits <= 2 * (int64_t)num_sms && a->seqlen_k / splits >= 4096;
   if (kernel == FA_KERNEL_DECODE && a->d == 128 && rows <= 16 && !pl->streamk && splits == 1 && !fx &&
       (int64_t)a->b * a->h_k >= 10 * (int64_t)num_sms) k.wide_cta = 2;      // >= 5 waves of 2 CTAs per SM: three smaller CTAs per SM
   // split workspace: lse block, padded to 4 floats so that the o block stays 16-byte aligned | o block | the arrival
