@@ -93,17 +93,17 @@ def test_paged_block_size_rule():
 
 
 @pytest.mark.parametrize("batch,ctx,want", [
-    (24, 1024, 1),      # the wave rule alone says 4: 768 pieces of 256 keys in 3 waves (38.5 us against 26.7 us)
-    (24, 4096, 3),      # pieces of >= 1024 keys may run to a second wave
-    (20, 4096, 3),      # the wave rule says 8 (2 blocks a piece): best-filling count among those that keep 1024 keys
-    (48, 1024, 1),      # 1.3 waves but pieces would be too short
-    (48, 4096, 2),      # 1.3 waves: the reference's rule never splits here (168 us -> 150 us)
-    (40, 4096, 3),
+    (24, 1024, 2),      # 192 units: 2 pieces each fill one wave of 3 CTAs per SM (the wave rule alone said 4 splits on 2 per SM: 38.5 us; now 24.6)
+    (24, 4096, 2),
+    (20, 4096, 2),
+    (48, 1024, 1),      # 384 units: one wave of the three-per-SM form, no split (60 -> 45 us)
+    (48, 4096, 1),
+    (40, 4096, 1),
     (64, 4096, 1), (256, 4096, 1),
 ])
-def test_decode_split_choice_follows_the_measured_rule(batch, ctx, want):
-    """fa_api.cu decode_splits(): the reference's wave rule with the two corrections of profiles/r02_decode_split_sweep.jsonl,
-    read back through the workspace size (partials of `s` pieces per unit)."""
+def test_decode_split_choice_follows_the_time_model(batch, ctx, want):
+    """fa_api.cu decode_choose(): grid form and split count of the d = 128 decode kernel from the time model fitted to
+    profiles/r02_decode_form_sweep.jsonl, read back through the workspace size (partials of `s` pieces per unit)."""
     if os.environ.get("FA_B200_STREAMK", "") not in ("", "0"):
         pytest.skip("balanced ranges forced on: no split count")
     P = _base()
@@ -114,6 +114,24 @@ def test_decode_split_choice_follows_the_measured_rule(batch, ctx, want):
     need = lib.fa_b200_workspace_bytes(C.byref(P), 2)
     assert need != C.c_size_t(-1).value, _cabi.last_error()
     got = 1 if need == 0 else (need - 16384 - 16) // (batch * 32 * (128 + 1) * 4)
+    assert got == want, (got, want, need)
+
+
+@pytest.mark.parametrize("batch,ctx,want", [(24, 1024, 1), (24, 4096, 3), (48, 4096, 2), (48, 1024, 1), (64, 4096, 1)])
+def test_decode_split_choice_other_head_dims_keep_the_corrected_wave_rule(batch, ctx, want):
+    """d != 128 has one grid form: decode_splits() — the reference's wave rule with the two corrections of
+    profiles/r02_decode_split_sweep.jsonl (split at 1.0-1.5 waves when pieces stay long; short pieces stay in one wave)."""
+    if os.environ.get("FA_B200_STREAMK", "") not in ("", "0"):
+        pytest.skip("balanced ranges forced on: no split count")
+    P = _base()
+    P.b, P.h, P.h_k, P.seqlen_k, P.num_splits, P.d = batch, 32, 8, ctx, 0, 64
+    P.q_row_stride, P.k_row_stride = 32 * 64, 8 * 64
+    P.v_row_stride, P.o_row_stride = 8 * 64, 32 * 64
+    P.q_head_stride = P.k_head_stride = P.v_head_stride = P.o_head_stride = 64
+    P.block_table, P.page_block_size, P.max_blocks_per_seq = 0x2000, 16, ctx // 16
+    need = lib.fa_b200_workspace_bytes(C.byref(P), 2)
+    assert need != C.c_size_t(-1).value, _cabi.last_error()
+    got = 1 if need == 0 else (need - 16384 - 16) // (batch * 32 * (64 + 1) * 4)
     assert got == want, (got, want, need)
 
 

@@ -76,6 +76,38 @@ static int decode_splits(int work, int slots, int n_blocks) {
   return s;
 }
 
+// d = 128, up to 16 packed rows: the decode kernel has two grid forms — 4 warps x 3 stages at 2 CTAs per SM and 4 x 2 at
+// 3 CTAs per SM (fa_decode.cu) — and which is faster depends on how units x splits falls on 2 or 3 slots per SM, so form
+// and split count are chosen TOGETHER by a small time model instead of the wave rule alone.  A launch is waves of
+// resident CTAs; in a wave of n CTAs a piece streams at min(what one CTA reaches with c CTAs on its SM, HBM / n); every
+// wave pays a fixed cost, a split launch a merge.  Constants fitted to a sweep of both forms x 7 split counts x 42
+// shapes on B200 (32-1024 units, 1024-16384 keys; profiles/r02_decode_form_sweep.jsonl): the model's pick is the
+// measured best or within 4.1 % of it (mean 0.5 %); against the wave rule it gains 8-25 % at 160-400 and 640-770
+// units (40 sequences x 8 kv heads x 1024 keys: 52.1 -> 39.3 us) and chooses the same counts for small batches.
+struct DecodeChoice { int form, splits; };
+static DecodeChoice decode_choose(int64_t units, int seqlen_k, int num_sms, bool allow_three_per_sm) {
+  static const float kCtaRate[2][3] = {{34.f, 27.f, 27.f}, {34.f, 27.f, 20.f}};   // GB/s per CTA with 1 / 2 / 3 CTAs on the SM
+  const float kHbm = 6900.f, kFix[2] = {3.0f, 3.5f}, kBase = 6.f, kMerge = 2.f, kPerSplit = 0.15f;   // GB/s, us
+  const int n_blocks = std::max(1, (seqlen_k + 255) / 256);
+  const float unit_bytes = (float)seqlen_k * 512.f;                                // K + V rows of 256 B
+  DecodeChoice best{0, 1}; float best_t = 1e30f;
+  for (int s = 1; s <= std::min(128, n_blocks); s++)
+    for (int f = 0; f < (allow_three_per_sm ? 2 : 1); f++) {
+      const int64_t slots = (int64_t)(f ? 3 : 2) * num_sms, pieces = units * s;
+      const float piece_bytes = unit_bytes / s;
+      auto wave = [&](int64_t n) {
+        const int c = (int)std::min<int64_t>((n + num_sms - 1) / num_sms, f ? 3 : 2);
+        const float rate = std::min(kCtaRate[f][c - 1], kHbm / (float)n);
+        return piece_bytes / rate * 1e-3f + kFix[f];
+      };
+      float t = kBase + (s > 1 ? kMerge + kPerSplit * s : 0.f);
+      if (pieces / slots) t += (float)(pieces / slots) * wave(slots);
+      if (pieces % slots) t += wave(pieces % slots);
+      if (t < best_t - 1e-4f) { best_t = t; best = DecodeChoice{f, s}; }
+    }
+  return best;
+}
+
 static int device_sms() {
   static int sms[64] = {0};
   int dev = 0;
@@ -159,6 +191,7 @@ struct Plan {
   bool streamk;                // decode kernel in its balanced-range form (fa_decode_streamk_kernel)
   int sk_slots;                // ... piece slots of its partial pool
   int mixed_splits;            // mixed varlen batch: split count of the decode half (>= 1)
+  int mixed_form;              // ... and its grid form (KParams::wide_cta of the 16-row launch: 0 or 2)
   size_t mixed_part_off;       // ... byte offset of its partials in the workspace (behind the prefill work list)
   size_t mixed_lse_floats;
 };
@@ -314,7 +347,7 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   // The reference consults its heuristic in mha_fwd (:375-377), in varlen only for GQA-packed
   // decode (:618-623) and in kvcache with the caller's num_splits (:903-905).  We split only in
   // the two kernels that write partials, sized for 2 resident CTAs per SM.
-  int splits = 1;
+  int splits = 1, decode_form = 0;
   const bool may_split = kernel != FA_KERNEL_TC5_PREFILL &&
                          (op == OP_KVCACHE || op == OP_FWD || (op == OP_VARLEN && a->seqlen_q == 1));
   if (may_split && a->seqlen_k > 0) {
@@ -325,8 +358,12 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
       const int n_blocks = (a->seqlen_k + blk - 1) / blk;
       const int work = kernel == FA_KERNEL_DECODE ? a->b * a->h_k
                                                   : a->b * a->h * ((a->seqlen_q + 63) / 64);
-      splits = kernel == FA_KERNEL_DECODE ? decode_splits(work, num_sms * 2, n_blocks)
-                                          : fa_b200_num_splits_heuristic(work, num_sms * 2, n_blocks, 128);
+      if (kernel == FA_KERNEL_DECODE && a->d == 128 && rows <= 16 && !fx) {
+        const DecodeChoice c = decode_choose(work, a->seqlen_k, num_sms, true);
+        splits = c.splits; decode_form = c.form;
+      } else
+        splits = kernel == FA_KERNEL_DECODE ? decode_splits(work, num_sms * 2, n_blocks)
+                                            : fa_b200_num_splits_heuristic(work, num_sms * 2, n_blocks, 128);
     }
     FA_CHECK(splits <= 128, "num_splits > 128 not supported");                         // :217
   }
@@ -353,8 +390,7 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   // and pays its larger fixed cost (8 sequences x 1024 keys: 16.4 -> 18.2 us), hence the high bar of 4096 keys per piece.
   k.wide_cta = kernel == FA_KERNEL_DECODE && a->d == 128 && rows <= 16 && !pl->streamk && splits >= 1 &&
                (int64_t)a->b * a->h_k * splits <= 2 * (int64_t)num_sms && a->seqlen_k / splits >= 4096;
-  if (kernel == FA_KERNEL_DECODE && a->d == 128 && rows <= 16 && !pl->streamk && splits == 1 && !fx &&
-      (int64_t)a->b * a->h_k >= 10 * (int64_t)num_sms) k.wide_cta = 2;      // >= 5 waves of 2 CTAs per SM: three smaller CTAs per SM
+  if (decode_form == 1 && !pl->streamk) k.wide_cta = 2;                     // three smaller CTAs per SM (decode_choose)
   // split workspace: lse block, padded to 4 floats so that the o block stays 16-byte aligned | o block | the arrival
   // counters of the decode kernel's in-kernel merge (when they are not part of a fused_exchange allocation)
   const size_t part_rows = pl->streamk ? (size_t)pl->sk_slots * k.sk_rows : (size_t)splits * a->b * a->h * std::max(a->seqlen_q, 1);
@@ -365,7 +401,7 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
   pl->counters_in_head = (size_t)a->b * a->h_k * sizeof(int) <= FA_B200_WS_HEAD_BYTES;
   pl->ws_bytes = splits > 1 ? FA_B200_WS_HEAD_BYTES + (pl->lse_floats + pl->o_floats) * sizeof(float) +
                               ((pl->fused_tail && !fx && !pl->counters_in_head) ? (size_t)a->b * a->h_k * sizeof(int) : 0) : 0;
-  pl->mixed_splits = 1; pl->mixed_part_off = 0; pl->mixed_lse_floats = 0;
+  pl->mixed_splits = 1; pl->mixed_part_off = 0; pl->mixed_lse_floats = 0; pl->mixed_form = 0;
   if (kernel == FA_KERNEL_TC5_PREFILL) {
     if (op == OP_VARLEN) FA_CHECK(a->total_q > 0, "total_q (rows of q) must be given for varlen_fwd");
     pl->ws_bytes = tc5_workspace_bytes(k, a->total_q, num_sms);    // cost-sorted work list of the persistent kernel
@@ -376,7 +412,12 @@ static int make_plan(const FaFwdParams* a, int op, Plan* pl) {
     // sequences are short is only known on the device: the count is taken as if all were.
     pl->sk_slots = 0;
     if (pl->decode_rows > 0 && a->seqlen_k > 0 && (size_t)a->b * a->h_k * sizeof(int) <= FA_B200_WS_HEAD_BYTES) {
-      const int ms = fa_b200_num_splits_heuristic(a->b * a->h_k, num_sms * 2, (a->seqlen_k + 255) / 256, 8);
+      int ms = fa_b200_num_splits_heuristic(a->b * a->h_k, num_sms * 2, (a->seqlen_k + 255) / 256, 8);
+      pl->mixed_form = 0;
+      if (a->d == 128 && k.group <= 16) {           // grid form and count together, as for a kvcache decode (decode_choose)
+        const DecodeChoice c = decode_choose((int64_t)a->b * a->h_k, a->seqlen_k, num_sms, true);
+        ms = std::min(c.splits, 8); pl->mixed_form = c.form;
+      }
 #ifndef FA_NO_STREAMK
       if (a->b <= 512 && (int64_t)a->b * a->h_k < 4 * (int64_t)num_sms * 2 && streamk_wanted((int64_t)a->b * a->h_k, num_sms, true)) {
         // few units: the balanced-range form of the decode kernel (see the kvcache case above); one pool of piece slots
@@ -494,7 +535,9 @@ static int run_plan_impl(FaFwdParams* a, int op, void* stream_) {
         }
         if (g <= lo_rows) {
           kd.min_rows = 0; kd.max_rows = lo_rows;
+          kd.wide_cta = (pl.mixed_form == 1 && pl.sk_slots == 0) ? 2 : 0;
           e = launch_decode(kd, pl.is_bf16, ds);
+          kd.wide_cta = 0;
           a->launches += 1;
         }
         if (e == cudaSuccess && second) {
