@@ -51,7 +51,8 @@ extern "C" int fa_b200_num_splits_heuristic(int work, int num_sms, int num_n_blo
   return 1;
 }
 
-// Decode kernel: the rule above with two corrections measured on B200 (profiles/r02_decode_split_sweep.jsonl: explicit
+// Decode kernel, every shape that decode_choose() below does not cover (d != 128, 17-32 packed rows, sharded calls): the
+// rule above with two corrections measured on B200 (profiles/r02_decode_split_sweep.jsonl: explicit
 // split counts against the automatic one, 20-256 sequences x 8 kv heads; slots = 2 resident CTAs per SM, blocks of 256
 // keys).  (1) 1.0-1.5 waves of units (the reference never splits above 0.8 waves): the second wave runs almost empty, so
 // 2-4 pieces per unit are taken when they fill the waves better AND a piece keeps >= 1024 keys (48 sequences: 4096 keys
